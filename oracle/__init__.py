@@ -161,3 +161,80 @@ class Ctx:
                 self.h = None
         except Exception:
             pass
+
+    # ---- numpy-level conveniences (each is one call into the C oracle) ----
+    def ntt(self, a, mod_idx, inverse=False):
+        a = np.array(a, dtype=np.uint64).reshape(len(mod_idx), self.N).copy()
+        f = self.L.orc_intt_many if inverse else self.L.orc_ntt_many
+        f(self.h, ints(mod_idx), len(mod_idx), P(a))
+        return a
+
+    def baseconv(self, a, src, dst, centered=False):
+        a = np.ascontiguousarray(a, dtype=np.uint64).reshape(len(src), self.N)
+        out = np.empty((len(dst), self.N), dtype=np.uint64)
+        self.L.orc_baseconv(self.h, ints(src), len(src), ints(dst), len(dst), P(a), P(out), 1 if centered else 0)
+        return out
+
+    def num_digits(self, level):
+        return int(self.L.orc_num_digits(self.h, level))
+
+    def galois_element(self, rot):
+        return int(self.L.orc_galois_element(self.h, rot))
+
+    def automorphism_ntt(self, a, gal_el):
+        a = np.ascontiguousarray(a, dtype=np.uint64).reshape(-1, self.N)
+        out = np.empty_like(a)
+        for i in range(a.shape[0]):
+            self.L.orc_automorphism_ntt(self.h, gal_el, P(a[i]), P(out[i]))
+        return out
+
+    def decompose(self, level, c1):
+        c1 = np.ascontiguousarray(c1, dtype=np.uint64).reshape(level + 1, self.N)
+        out = np.empty((self.num_digits(level), level + 1 + self.nP, self.N), dtype=np.uint64)
+        self.L.orc_decompose(self.h, level, P(c1), P(out))
+        return out
+
+    def inner_product(self, level, digits, evk):
+        W = level + 1 + self.nP
+        a0 = np.empty((W, self.N), dtype=np.uint64)
+        a1 = np.empty((W, self.N), dtype=np.uint64)
+        digits = np.ascontiguousarray(digits, dtype=np.uint64)
+        evk = np.ascontiguousarray(evk, dtype=np.uint64)
+        self.L.orc_inner_product(self.h, level, P(digits), P(evk), P(a0), P(a1))
+        return a0, a1
+
+    def moddown(self, level, acc):
+        acc = np.ascontiguousarray(acc, dtype=np.uint64).reshape(level + 1 + self.nP, self.N)
+        out = np.empty((level + 1, self.N), dtype=np.uint64)
+        self.L.orc_moddown(self.h, level, P(acc), P(out))
+        return out
+
+    def keyswitch(self, level, c1, evk):
+        c1 = np.ascontiguousarray(c1, dtype=np.uint64).reshape(level + 1, self.N)
+        evk = np.ascontiguousarray(evk, dtype=np.uint64)
+        o0 = np.empty((level + 1, self.N), dtype=np.uint64)
+        o1 = np.empty((level + 1, self.N), dtype=np.uint64)
+        self.L.orc_keyswitch(self.h, level, P(c1), P(evk), P(o0), P(o1))
+        return np.stack([o0, o1])
+
+    def rescale(self, level, a):
+        a = np.ascontiguousarray(a, dtype=np.uint64).reshape(level + 1, self.N)
+        out = np.empty((level, self.N), dtype=np.uint64)
+        self.L.orc_rescale(self.h, level, P(a), P(out))
+        return out
+
+    def elementwise(self, op, a, b=None):
+        a = np.ascontiguousarray(a, dtype=np.uint64).reshape(-1, self.N)
+        out = np.empty_like(a)
+        if b is not None:
+            b = np.ascontiguousarray(b, dtype=np.uint64).reshape(-1, self.N)
+        for i in range(a.shape[0]):
+            if op == "neg":
+                self.L.orc_neg(self.h, i, P(a[i]), P(out[i]))
+            else:
+                getattr(self.L, "orc_" + op)(self.h, i, P(a[i]), P(b[i]), P(out[i]))
+        return out
+
+    def uniform_poly(self, rng, mod_idx):
+        """[len(mod_idx)][N] with limb i uniform in [0, q_{mod_idx[i]}) from a numpy Generator."""
+        return np.stack([rng.integers(0, self.moduli[m], size=self.N, dtype=np.uint64) for m in mod_idx])

@@ -1,0 +1,200 @@
+// capi_raw.cu -- primitive-level C ABI ("B200_*"): contexts over explicit modulus chains, batched NTT, base
+// conversion, key switching, rescale on host or device buffers.  This is the surface the primitive sweep
+// (BASELINE.json configs[4]) and the kernel parity tests drive; the Orion-facing surface with the Go shim's
+// export names lives in capi.cu.  Declarations + reference citations: include/orion_b200.h.
+#include "evaluator.h"
+#include "../../include/orion_b200.h"
+
+using namespace ob;
+
+namespace {
+struct RawCtx {
+    std::unique_ptr<Context> ctx;
+    std::unique_ptr<PolyEvaluator> ev;
+};
+RawCtx* R(void* h) { OB_CHECK(h != nullptr, "null context handle"); return (RawCtx*)h; }
+
+void h2d(void* d, const void* h, size_t bytes) { OB_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, stream())); }
+void d2h(void* h, const void* d, size_t bytes) {
+    OB_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+}
+cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
+}  // namespace
+
+extern "C" {
+
+int B200_GenModuli(const int* logQ, int nQ, const int* logP, int nP, int logNthRoot, uint64_t* Q, uint64_t* P) {
+    std::vector<int> lq(logQ, logQ + nQ), lp(logP, logP + nP);
+    std::vector<u64> q, p;
+    gen_moduli(lq, lp, logNthRoot, q, p);
+    for (int i = 0; i < nQ; ++i) Q[i] = q[i];
+    for (int i = 0; i < nP; ++i) P[i] = p[i];
+    return 0;
+}
+uint64_t B200_FindPsi(uint64_t q, uint64_t nthroot) { return find_psi(q, nthroot); }
+
+int B200_DeviceCount(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+void* B200_NewContext(int logN, const uint64_t* Q, int nQ, const uint64_t* P, int nP) {
+    ensure_device();
+    auto* r = new RawCtx();
+    r->ctx = std::make_unique<Context>(logN, std::vector<u64>(Q, Q + nQ), std::vector<u64>(P, P + nP));
+    r->ev = std::make_unique<PolyEvaluator>(*r->ctx);
+    return r;
+}
+void B200_DeleteContext(void* h) {
+    if (!h) return;
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    delete (RawCtx*)h;
+}
+uint64_t B200_ContextPsi(void* h, int idx) { return R(h)->ctx->psi[idx]; }
+
+void B200_Sync(void) { OB_CUDA(cudaStreamSynchronize(stream())); }
+unsigned long long B200_LaunchCount(void) { return g_launches; }
+void* B200_Stream(void) { return (void*)stream(); }
+void B200_TimerStart(void) {
+    if (!g_ev0) { OB_CUDA(cudaEventCreate(&g_ev0)); OB_CUDA(cudaEventCreate(&g_ev1)); }
+    OB_CUDA(cudaEventRecord(g_ev0, stream()));
+}
+float B200_TimerStopMs(void) {
+    OB_CUDA(cudaEventRecord(g_ev1, stream()));
+    OB_CUDA(cudaEventSynchronize(g_ev1));
+    float ms = 0; OB_CUDA(cudaEventElapsedTime(&ms, g_ev0, g_ev1));
+    return ms;
+}
+
+void* B200_DevAlloc(size_t words) { ensure_device(); void* p; OB_CUDA(cudaMallocAsync(&p, words * 8, stream())); return p; }
+void B200_DevFree(void* p) { if (p) OB_CUDA(cudaFreeAsync(p, stream())); }
+void B200_Upload(void* dev, const uint64_t* host, size_t words) { h2d(dev, host, words * 8); OB_CUDA(cudaStreamSynchronize(stream())); }
+void B200_UploadAsync(void* dev, const uint64_t* host, size_t words) { h2d(dev, host, words * 8); }
+void B200_Download(uint64_t* host, const void* dev, size_t words) { d2h(host, dev, words * 8); }
+void* B200_HostAllocPinned(size_t words) { void* p; OB_CUDA(cudaMallocHost(&p, words * 8)); return p; }
+void B200_HostFreePinned(void* p) { if (p) OB_CUDA(cudaFreeHost(p)); }
+
+// ---- NTT ----
+static NttPlan contiguous_plan(RawCtx* r, const int* mod_idx, int n) {
+    std::vector<LimbDesc> l(n);
+    for (int i = 0; i < n; ++i) {
+        OB_CHECK(mod_idx[i] >= 0 && mod_idx[i] < r->ctx->nmod, "modulus index out of range");
+        l[i] = LimbDesc{(uint32_t)i, (uint32_t)i, (uint32_t)mod_idx[i], 0};
+    }
+    return make_ntt_plan(*r->ctx, l);
+}
+void B200_NTTDev(void* h, const void* in, void* out, const int* mod_idx, int n, int inverse) {
+    RawCtx* r = R(h);
+    NttPlan p = contiguous_plan(r, mod_idx, n);
+    if (inverse) ntt_inverse(*r->ctx, (const u64*)in, (u64*)out, p);
+    else ntt_forward(*r->ctx, (const u64*)in, (u64*)out, p);
+}
+void B200_NTT(void* h, const uint64_t* in, uint64_t* out, const int* mod_idx, int n, int inverse) {
+    RawCtx* r = R(h);
+    size_t bytes = (size_t)n * r->ctx->N * 8;
+    DevBuf d(bytes);
+    h2d(d.p, in, bytes);
+    B200_NTTDev(h, d.p, d.p, mod_idx, n, inverse);
+    d2h(out, d.p, bytes);
+}
+
+// ---- base conversion (coefficient domain) ----
+void B200_BaseConv(void* h, const int* src, int ns, const int* dst, int nd, const uint64_t* in, uint64_t* out, int centered) {
+    RawCtx* r = R(h);
+    size_t N = r->ctx->N;
+    std::vector<int> s(src, src + ns), d(dst, dst + nd), off(nd);
+    for (int i = 0; i < nd; ++i) off[i] = i;
+    BaseConvPlan p = make_baseconv_plan(*r->ctx, s, d, off);
+    DevBuf di(ns * N * 8), dout(nd * N * 8);
+    h2d(di.p, in, ns * N * 8);
+    base_convert(*r->ctx, p, di.u(), dout.u(), centered != 0);
+    d2h(out, dout.p, nd * N * 8);
+}
+
+// ---- automorphism (NTT domain), n limbs ----
+void B200_AutomorphismNTT(void* h, uint64_t galEl, const uint64_t* in, uint64_t* out, int n) {
+    RawCtx* r = R(h);
+    size_t bytes = (size_t)n * r->ctx->N * 8;
+    DevBuf a(bytes), b(bytes);
+    h2d(a.p, in, bytes);
+    automorphism_ntt(*r->ctx, a.u(), b.u(), n, r->ctx->galois_index(galEl));
+    d2h(out, b.p, bytes);
+}
+uint64_t B200_GaloisElement(void* h, int rot) { return R(h)->ctx->galois_element(rot); }
+
+// ---- evaluation keys: host standard form [beta_max][2][nQ+nP][N] -> device Montgomery form ----
+void* B200_EvkToDevice(void* h, const uint64_t* evk_host) {
+    RawCtx* r = R(h); Context& c = *r->ctx;
+    int beta = c.num_digits(c.nQ - 1);
+    size_t words = (size_t)beta * 2 * c.nmod * c.N;
+    u64* d = (u64*)B200_DevAlloc(words);
+    h2d(d, evk_host, words * 8);
+    // limbs per "poly" = nmod with L = nQ  ->  chain index = limb index
+    to_montgomery(c, d, d, beta * 2, c.nmod, c.nQ);
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    return d;
+}
+
+// ---- key switch: out[2][L][N] = KeySwitch(c1) (+ addend c0 on polynomial 0 when addend != NULL) ----
+void B200_KeySwitchDev(void* h, int level, const void* c1, const void* evk_dev, const void* addend_c0, void* out) {
+    RawCtx* r = R(h);
+    r->ev->keyswitch(level, (const u64*)c1, (const u64*)evk_dev, (const u64*)addend_c0, level + 1, addend_c0 ? 1 : 0,
+                     (u64*)out, level + 1);
+}
+void B200_KeySwitch(void* h, int level, const uint64_t* c1, const void* evk_dev, const uint64_t* addend_c0, uint64_t* out) {
+    RawCtx* r = R(h);
+    size_t LN = (size_t)(level + 1) * r->ctx->N;
+    DevBuf d1(LN * 8), d0(addend_c0 ? LN * 8 : 0), dout(2 * LN * 8);
+    h2d(d1.p, c1, LN * 8);
+    if (addend_c0) h2d(d0.p, addend_c0, LN * 8);
+    B200_KeySwitchDev(h, level, d1.p, evk_dev, addend_c0 ? d0.p : nullptr, dout.p);
+    d2h(out, dout.p, 2 * LN * 8);
+}
+
+// ---- pieces of the key switch, for stage-by-stage parity ----
+void B200_Decompose(void* h, int level, const uint64_t* c1, uint64_t* digits /* [beta][W][N], own limbs = c1 */) {
+    RawCtx* r = R(h); Context& c = *r->ctx;
+    int L = level + 1, K = c.nP, W = L + K, beta = c.num_digits(level);
+    size_t N = c.N;
+    DevBuf d1(L * N * 8), dg(r->ev->digits_words(level) * 8);
+    h2d(d1.p, c1, L * N * 8);
+    r->ev->decompose(level, d1.u(), dg.u());
+    for (int j = 0; j < beta; ++j)                       // fill own-digit limbs so the host sees the full digit
+        for (int t = j * K; t < std::min((j + 1) * K, L); ++t)
+            OB_CUDA(cudaMemcpyAsync(dg.u() + ((size_t)j * W + t) * N, d1.u() + (size_t)t * N, N * 8, cudaMemcpyDeviceToDevice, stream()));
+    d2h(digits, dg.p, r->ev->digits_words(level) * 8);
+}
+void B200_ModDown(void* h, int level, const uint64_t* accQP /* [W][N] */, uint64_t* outQ /* [L][N] */) {
+    RawCtx* r = R(h); Context& c = *r->ctx;
+    int L = level + 1, W = L + c.nP; size_t N = c.N;
+    DevBuf a(W * N * 8), o(L * N * 8);
+    h2d(a.p, accQP, W * N * 8);
+    r->ev->moddown(level, a.u(), 1, nullptr, 0, 0, o.u(), L);
+    d2h(outQ, o.p, L * N * 8);
+}
+
+// ---- rescale: in [polys][level+1][N] -> out [polys][level][N] ----
+void B200_RescaleDev(void* h, int level, const void* in, void* out, int polys) {
+    R(h)->ev->rescale(level, (const u64*)in, level + 1, (u64*)out, level, polys);
+}
+void B200_Rescale(void* h, int level, const uint64_t* in, uint64_t* out, int polys) {
+    RawCtx* r = R(h); size_t N = r->ctx->N;
+    DevBuf a((size_t)polys * (level + 1) * N * 8), o((size_t)polys * level * N * 8);
+    h2d(a.p, in, a.bytes);
+    B200_RescaleDev(h, level, a.p, o.p, polys);
+    d2h(out, o.p, o.bytes);
+}
+
+// ---- element-wise on host buffers: op 0 add, 1 sub, 2 neg, 3 mul;  n limbs with chain indices = 0..n-1 ----
+void B200_Elementwise(void* h, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, int n) {
+    RawCtx* r = R(h); size_t N = r->ctx->N;
+    DevBuf da(n * N * 8), db(n * N * 8), dout(n * N * 8);
+    h2d(da.p, a, n * N * 8);
+    if (b) h2d(db.p, b, n * N * 8);
+    ew_binary(*r->ctx, (EwOp)op, da.u(), n, db.u(), n, 1, dout.u(), n, 1, n, n);
+    d2h(out, dout.p, n * N * 8);
+}
+
+}  // extern "C"

@@ -1,0 +1,57 @@
+// common.h -- shared host-side declarations for liborion_b200.so (B200 / sm_100a CKKS backend).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "modarith.cuh"
+
+namespace ob {
+
+// The reference's Go shim panics (process abort) on any error (LG/evaluator.go:52-54); this backend
+// does the same: print and abort.  There is no CPU fallback anywhere in this library.
+[[noreturn]] inline void fatal(const char* file, int line, const std::string& msg) {
+    std::fprintf(stderr, "orion_b200 fatal: %s  (%s:%d)\n", msg.c_str(), file, line);
+    std::fflush(stderr);
+    std::abort();
+}
+#define OB_FATAL(msg) ::ob::fatal(__FILE__, __LINE__, (msg))
+#define OB_CHECK(cond, msg) do { if (!(cond)) OB_FATAL(std::string("check failed: " #cond " -- ") + (msg)); } while (0)
+#define OB_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) \
+    OB_FATAL(std::string("CUDA error: ") + cudaGetErrorString(e__) + " in " #call); } while (0)
+
+// launch counter: every kernel of this library goes through OB_LAUNCH so bench.py can report gpu_launches
+extern unsigned long long g_launches;
+#define OB_LAUNCH(kernel, grid, block, smem, stream, ...) do { \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__); ::ob::g_launches++; \
+    OB_CUDA(cudaPeekAtLastError()); } while (0)
+
+cudaStream_t stream();          // the library's single compute stream
+void ensure_device();           // aborts loudly when no CUDA device is usable
+
+// stream-ordered device buffer (cudaMallocAsync pool with an unlimited release threshold -> frees are cached)
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    DevBuf() {}
+    explicit DevBuf(size_t n) { alloc(n); }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept { if (this != &o) { release(); p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; } return *this; }
+    ~DevBuf() { release(); }
+    void alloc(size_t n);
+    void release();
+    u64* u() const { return (u64*)p; }
+    template <class T> T* as() const { return (T*)p; }
+};
+
+// one limb of a batched kernel launch: where it is read, where it is written, which modulus
+struct LimbDesc { uint32_t in_off, out_off, mod, aux; };   // offsets in units of N words
+
+}  // namespace ob

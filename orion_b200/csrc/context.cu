@@ -1,0 +1,283 @@
+// context.cu -- parameter generation and HBM-resident tables.
+#include "context.h"
+#include <algorithm>
+
+namespace ob {
+
+unsigned long long g_launches = 0;
+static cudaStream_t g_stream = nullptr;
+static bool g_dev_ok = false;
+
+void ensure_device() {
+    if (g_dev_ok) return;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        OB_FATAL("no CUDA device visible: liborion_b200 has no CPU path (" + std::string(cudaGetErrorString(e)) + ")");
+    int dev = 0;
+    if (const char* s = std::getenv("ORION_B200_DEVICE")) dev = std::atoi(s);
+    else if (const char* s2 = std::getenv("LOCAL_RANK")) dev = std::atoi(s2) % n;
+    OB_CUDA(cudaSetDevice(dev));
+    OB_CUDA(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+    cudaMemPool_t pool;
+    OB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    uint64_t thr = UINT64_MAX;
+    OB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    g_dev_ok = true;
+}
+cudaStream_t stream() { ensure_device(); return g_stream; }
+
+void DevBuf::alloc(size_t n) {
+    release();
+    if (n == 0) return;
+    OB_CUDA(cudaMallocAsync(&p, n, stream()));
+    bytes = n;
+}
+void DevBuf::release() {
+    if (p) { cudaFreeAsync(p, g_stream); p = nullptr; bytes = 0; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host number theory
+// ------------------------------------------------------------------------------------------------
+u64 mulmod_u64(u64 a, u64 b, u64 q) { return (u64)(((u128)a * b) % q); }
+u64 powmod_u64(u64 a, u64 e, u64 q) {
+    u64 r = 1 % q; a %= q;
+    for (; e; e >>= 1) { if (e & 1) r = mulmod_u64(r, a, q); a = mulmod_u64(a, a, q); }
+    return r;
+}
+u64 invmod_u64(u64 a, u64 q) { return powmod_u64(a % q, q - 2, q); }
+u64 shoup_companion(u64 w, u64 q) { return (u64)(((u128)w << 64) / q); }
+
+bool is_prime_u64(u64 n) {
+    if (n < 2) return false;
+    for (u64 p : {2ull, 3ull, 5ull, 7ull, 11ull, 13ull, 17ull, 19ull, 23ull, 29ull, 31ull, 37ull}) {
+        if (n == p) return true;
+        if (n % p == 0) return false;
+    }
+    u64 d = n - 1; int s = 0;
+    while ((d & 1) == 0) { d >>= 1; ++s; }
+    for (u64 a : {2ull, 3ull, 5ull, 7ull, 11ull, 13ull, 17ull, 19ull, 23ull, 29ull, 31ull, 37ull}) {
+        u64 x = powmod_u64(a, d, n);
+        if (x == 1 || x == n - 1) continue;
+        bool composite = true;
+        for (int r = 1; r < s && composite; ++r) { x = mulmod_u64(x, x, n); if (x == n - 1) composite = false; }
+        if (composite) return false;
+    }
+    return true;
+}
+
+// NTT-friendly primes (= 1 mod nthroot) alternating above / below 2^bits, nearest first
+// (the order Lattigo's NextAlternatingPrime produces; LG/scheme.go:57-65 reaches it via GenModuli).
+std::vector<u64> gen_ntt_primes(int bits, u64 nthroot, int count, const std::vector<u64>& skip) {
+    std::vector<u64> out;
+    u64 up = (1ull << bits) + 1, down = (1ull << bits) + 1 - nthroot;
+    bool up_ok = true, down_ok = true;
+    auto take = [&](u64 c) {
+        if (!is_prime_u64(c)) return;
+        if (std::find(skip.begin(), skip.end(), c) != skip.end()) return;
+        if (std::find(out.begin(), out.end(), c) != out.end()) return;
+        out.push_back(c);
+    };
+    while ((int)out.size() < count) {
+        OB_CHECK(up_ok || down_ok, "ran out of NTT-friendly primes of this size");
+        if (up_ok) {
+            if (up >> (bits + 1)) up_ok = false;
+            else { u64 c = up; up += nthroot; take(c); }
+        }
+        if ((int)out.size() >= count) break;
+        if (down_ok) {
+            if (down < nthroot || (down >> (bits - 1)) == 0) down_ok = false;
+            else { u64 c = down; down -= nthroot; take(c); }
+        }
+    }
+    return out;
+}
+
+void gen_moduli(const std::vector<int>& logQ, const std::vector<int>& logP, int log_nthroot,
+                std::vector<u64>& Q, std::vector<u64>& P) {
+    std::map<int, int> need;
+    for (int b : logQ) need[b]++;
+    for (int b : logP) need[b]++;
+    std::map<int, std::vector<u64>> pool;
+    for (auto& kv : need) {
+        OB_CHECK(kv.first >= 10 && kv.first <= 61, "prime size must be within 10..61 bits");
+        pool[kv.first] = gen_ntt_primes(kv.first, 1ull << log_nthroot, kv.second, {});
+    }
+    std::map<int, int> used;
+    Q.clear(); P.clear();
+    for (int b : logQ) Q.push_back(pool[b][used[b]++]);
+    for (int b : logP) P.push_back(pool[b][used[b]++]);
+}
+
+static void factor_distinct(u64 n, std::vector<u64>& f) {
+    auto push = [&](u64 p) { if (std::find(f.begin(), f.end(), p) == f.end()) f.push_back(p); };
+    for (u64 p = 2; p < 4096 && p * p <= n; ++p)
+        if (n % p == 0) { push(p); while (n % p == 0) n /= p; }
+    if (n == 1) return;
+    if (is_prime_u64(n)) { push(n); return; }
+    // Pollard rho (Brent-free, Floyd) for the remaining cofactor
+    u64 d = n;
+    for (u64 c = 1; d == n; ++c) {
+        u64 x = 2, y = 2; d = 1;
+        while (d == 1) {
+            x = (mulmod_u64(x, x, n) + c) % n;
+            y = (mulmod_u64(y, y, n) + c) % n; y = (mulmod_u64(y, y, n) + c) % n;
+            u64 a = x > y ? x - y : y - x, b = n;
+            while (b) { u64 t = a % b; a = b; b = t; }
+            d = a;
+        }
+    }
+    factor_distinct(d, f); factor_distinct(n / d, f);
+}
+u64 primitive_root(u64 q) {
+    std::vector<u64> f; factor_distinct(q - 1, f);
+    for (u64 g = 3;; ++g) {
+        bool ok = true;
+        for (u64 p : f) if (powmod_u64(g, (q - 1) / p, q) == 1) { ok = false; break; }
+        if (ok) return g;
+    }
+}
+u64 find_psi(u64 q, u64 nthroot) { return powmod_u64(primitive_root(q), (q - 1) / nthroot, q); }
+
+ModConst make_modconst(u64 q) {
+    ModConst m; std::memset(&m, 0, sizeof(m));
+    OB_CHECK(q < (1ull << 62) && (q & 1), "modulus must be odd and below 2^62");
+    m.q = q; m.bits = 64 - __builtin_clzll(q);
+    m.mu = (u64)((((u128)1) << (62 + m.bits)) / q);
+    u64 inv = 1;                                   // Newton iteration for q^-1 mod 2^64
+    for (int i = 0; i < 6; ++i) inv *= 2 - q * inv;
+    m.qinv_neg = (u64)(0 - inv);
+    m.r1 = (u64)((((u128)1) << 64) % q); m.r1_sh = shoup_companion(m.r1, q);
+    m.r2 = mulmod_u64(m.r1, m.r1, q);    m.r2_sh = shoup_companion(m.r2, q);
+    m.qd = (double)q;
+    return m;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Context
+// ------------------------------------------------------------------------------------------------
+static uint32_t bitrev_u32(uint32_t x, int bits) {
+    uint32_t r = 0;
+    for (int i = 0; i < bits; ++i) { r = (r << 1) | (x & 1); x >>= 1; }
+    return r;
+}
+
+template <class T>
+static void upload(DevBuf& d, const std::vector<T>& h) {
+    d.alloc(h.size() * sizeof(T));
+    if (!h.empty()) {
+        OB_CUDA(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, stream()));
+        OB_CUDA(cudaStreamSynchronize(stream()));     // h may be a temporary
+    }
+}
+
+Context::Context(int logN_, const std::vector<u64>& Q, const std::vector<u64>& P) {
+    ensure_device();
+    logN = logN_; N = 1 << logN; nQ = (int)Q.size(); nP = (int)P.size(); nmod = nQ + nP;
+    OB_CHECK(logN >= 10 && logN <= 17, "logN must be within 10..17");
+    OB_CHECK(nmod <= 64, "at most 64 moduli");
+    mod = Q; mod.insert(mod.end(), P.begin(), P.end());
+    std::vector<ulonglong2> twf((size_t)nmod * N), twi((size_t)nmod * N), ninv(nmod);
+    for (int m = 0; m < nmod; ++m) {
+        u64 q = mod[m];
+        OB_CHECK((q - 1) % (2ull * N) == 0, "modulus is not 1 mod 2N");
+        mc.push_back(make_modconst(q));
+        u64 ps = find_psi(q, 2ull * N), psi_inv = invmod_u64(ps, q);
+        psi.push_back(ps);
+        u64 pf = 1, pi = 1;
+        for (int i = 0; i < N; ++i) {
+            uint32_t j = bitrev_u32((uint32_t)i, logN);
+            twf[(size_t)m * N + j] = make_ulonglong2(pf, shoup_companion(pf, q));
+            twi[(size_t)m * N + j] = make_ulonglong2(pi, shoup_companion(pi, q));
+            pf = mulmod_u64(pf, ps, q); pi = mulmod_u64(pi, psi_inv, q);
+        }
+        u64 ni = invmod_u64((u64)N % q, q);
+        ninv[m] = make_ulonglong2(ni, shoup_companion(ni, q));
+    }
+    upload(d_mc, mc); upload(d_tw_fwd, twf); upload(d_tw_inv, twi); upload(d_ninv, ninv);
+
+    std::vector<ulonglong2> pinv(nQ), pmodq(nQ), qlinv((size_t)nQ * nQ);
+    for (int i = 0; i < nQ; ++i) {
+        u64 q = mod[i], pm = 1;
+        for (int k = 0; k < nP; ++k) pm = mulmod_u64(pm, mod[nQ + k] % q, q);
+        u64 pi = invmod_u64(pm, q);
+        pinv[i] = make_ulonglong2(pi, shoup_companion(pi, q));
+        pmodq[i] = make_ulonglong2(pm, shoup_companion(pm, q));
+        for (int l = 0; l < nQ; ++l) {
+            u64 v = (l == i) ? 0 : invmod_u64(mod[l] % q, q);
+            qlinv[(size_t)l * nQ + i] = make_ulonglong2(v, shoup_companion(v, q));
+        }
+    }
+    upload(d_pinv, pinv); upload(d_pmodq, pmodq); upload(d_qlinv, qlinv);
+}
+
+Context::~Context() {}
+
+const LimbDesc* Context::limb_list(const std::vector<LimbDesc>& v) {
+    std::vector<uint32_t> key; key.reserve(v.size() * 4);
+    for (auto& d : v) { key.push_back(d.in_off); key.push_back(d.out_off); key.push_back(d.mod); key.push_back(d.aux); }
+    auto it = limb_cache_.find(key);
+    if (it == limb_cache_.end()) {
+        auto buf = std::make_unique<DevBuf>();
+        upload(*buf, v);
+        it = limb_cache_.emplace(std::move(key), std::move(buf)).first;
+    }
+    return it->second->as<LimbDesc>();
+}
+
+const BaseConv& Context::base_conv(const std::vector<int>& src, const std::vector<int>& dst) {
+    std::vector<int> key = src; key.push_back(-1); key.insert(key.end(), dst.begin(), dst.end());
+    auto it = bc_cache_.find(key);
+    if (it != bc_cache_.end()) return *it->second;
+    auto bc = std::make_unique<BaseConv>();
+    int ns = (int)src.size(), nd = (int)dst.size();
+    bc->ns = ns; bc->nd = nd; bc->h_src = src; bc->h_dst = dst;
+    std::vector<u64> inv(2 * ns), mat((size_t)ns * nd), negvq((size_t)nd * (ns + 1)), hs(ns), hd(nd);
+    for (int i = 0; i < ns; ++i) {
+        u64 qi = mod[src[i]], prod = 1;
+        for (int k = 0; k < ns; ++k) if (k != i) prod = mulmod_u64(prod, mod[src[k]] % qi, qi);
+        inv[2 * i] = invmod_u64(prod, qi); inv[2 * i + 1] = shoup_companion(inv[2 * i], qi);
+        hs[i] = mulmod_u64(qi - 1, (qi + 1) / 2, qi);                 // (Q-1)/2 mod q_i, Q = 0 mod q_i
+    }
+    for (int d = 0; d < nd; ++d) {
+        u64 p = mod[dst[d]], all = 1;
+        for (int i = 0; i < ns; ++i) {
+            u64 prod = 1;
+            for (int k = 0; k < ns; ++k) if (k != i) prod = mulmod_u64(prod, mod[src[k]] % p, p);
+            mat[(size_t)i * nd + d] = mulmod_u64(prod, mc[dst[d]].r1, p);
+            all = mulmod_u64(all, mod[src[i]] % p, p);
+        }
+        for (int v = 0; v <= ns; ++v) negvq[(size_t)d * (ns + 1) + v] = (p - mulmod_u64((u64)v, all, p)) % p;
+        hd[d] = mulmod_u64((all + p - 1) % p, (p + 1) / 2, p);
+    }
+    upload(bc->src_mod, src); upload(bc->dst_mod, dst);
+    upload(bc->inv, inv); upload(bc->mat, mat); upload(bc->negvq, negvq);
+    upload(bc->half_src, hs); upload(bc->half_dst, hd);
+    return *bc_cache_.emplace(std::move(key), std::move(bc)).first->second;
+}
+
+u64 Context::galois_element(int rot) const {
+    int ord = N / 2, k = ((rot % ord) + ord) % ord;
+    u64 g = 1, mask = 2ull * N - 1;
+    for (int i = 0; i < k; ++i) g = (g * 5) & mask;
+    return g;
+}
+
+const uint32_t* Context::galois_index(u64 galEl) {
+    auto it = gal_cache_.find(galEl);
+    if (it == gal_cache_.end()) {
+        std::vector<uint32_t> idx(N);
+        u64 mask = 2ull * N - 1;
+        for (int i = 0; i < N; ++i) {
+            u64 e = (galEl * (2ull * bitrev_u32(i, logN) + 1)) & mask;
+            idx[i] = bitrev_u32((uint32_t)((e - 1) >> 1), logN);
+        }
+        auto buf = std::make_unique<DevBuf>();
+        upload(*buf, idx);
+        it = gal_cache_.emplace(galEl, std::move(buf)).first;
+    }
+    return it->second->as<uint32_t>();
+}
+
+}  // namespace ob

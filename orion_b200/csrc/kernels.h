@@ -1,0 +1,48 @@
+// kernels.h -- launchers for the non-NTT kernels of the CKKS hot path (kernels.cu).
+// "QP layout at level l": limbs Q_0..Q_l followed by P_0..P_{nP-1}; W = l+1+nP limbs per polynomial.
+#pragma once
+#include "context.h"
+
+namespace ob {
+
+enum EwOp { EW_ADD = 0, EW_SUB = 1, EW_NEG = 2, EW_MUL = 3, EW_COPY = 4 };
+
+// out[p][t][x] = a[p][t][x] op b[(p % b_polys)][t][x];  polys x limbs x N words, limb t uses chain index
+// (t < L ? t : nQ + t - L).  a/b/out strides are given in limbs so operands at different levels can be mixed.
+void ew_binary(Context& c, EwOp op, const u64* a, int a_stride, const u64* b, int b_stride, int b_polys,
+               u64* out, int out_stride, int polys, int limbs, int L);
+// out = a * s_t  /  a + s_t   with one scalar per limb (host vector, residues < q_t); scalars[t]
+void ew_mul_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_stride, int polys, int limbs, int L,
+                   const std::vector<u64>& scalars);
+void ew_add_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_stride, int polys, int limbs, int L,
+                   const std::vector<u64>& scalars, int only_poly);
+// degree-2 tensor product: (d0,d1,d2) = (a0*b0, a0*b1 + a1*b0, a1*b1), L limbs each (chain index = limb)
+void tensor_product(Context& c, const u64* a, int a_stride, const u64* b, int b_stride, u64* out, int L);
+// NTT-domain automorphism: out[p][t][i] = in[p][t][idx[i]]
+void automorphism_ntt(Context& c, const u64* in, u64* out, int total_limbs, const uint32_t* idx);
+// to / from Montgomery form (x * 2^64 mod q), limbs laid out like ew_binary
+void to_montgomery(Context& c, const u64* in, u64* out, int polys, int limbs, int L);
+void from_montgomery(Context& c, const u64* in, u64* out, int polys, int limbs, int L);
+
+// ---- base conversion: in [ns][N] (coefficient domain, contiguous), out limb d written at out + out_off[d]*N ----
+struct BaseConvPlan { const BaseConv* bc = nullptr; const LimbDesc* out_off = nullptr; };
+BaseConvPlan make_baseconv_plan(Context& c, const std::vector<int>& src, const std::vector<int>& dst,
+                                const std::vector<int>& out_off);
+void base_convert(Context& c, const BaseConvPlan& p, const u64* in, u64* out, bool centered);
+
+// ---- key-switch inner product ----
+// acc[c][t][x] = sum_j digit_j[t][x] * evk[j][c][chain(t)][x]  (evk in Montgomery form, full-chain layout).
+// digit_j limb t is read from `digits + (j*W + t)*N` unless t belongs to digit j itself, in which case it is
+// read from c1_ntt + t*N.  gather != nullptr applies an NTT-domain automorphism to the digits on the fly.
+void ks_inner_product(Context& c, int level, const u64* c1_ntt, const u64* digits, const u64* evk,
+                      u64* acc /* [2][W][N] */, const uint32_t* gather, bool accumulate);
+
+// out[p][i][x] = (acc[p][i][x] - conv[p][i][x]) * P^-1 (+ addend[p][i][x])   i <= level; acc has stride W limbs
+void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
+                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys);
+
+// rescale helpers (level -> level-1): see evaluator.cu
+void rescale_prep(Context& c, int level, const u64* last_coeff /* [polys][N] */, u64* tmp /* [polys][level][N] */, int polys);
+void rescale_finish(Context& c, int level, const u64* in, int in_stride, const u64* tmp, u64* out, int out_stride, int polys);
+
+}  // namespace ob

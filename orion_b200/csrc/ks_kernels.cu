@@ -1,0 +1,192 @@
+// ks_kernels.cu -- key-switching kernels for sm_100a: RNS fast base conversion (ModUp per digit, ModDown),
+// the evaluation-key inner product, and the ModDown / rescale epilogues.
+//
+// Base conversion follows the Lattigo definition named in SURVEY.md section 8(a) a10 (float64 overflow
+// estimate, accumulated in source-limb order), NOT HEonGPU's float32 estimate
+// (HE/src/heongpu/lib/kernel/switchkey.cu:829-845):
+//     y_i = x_i * (Q_S/q_i)^-1 mod q_i,  v = (u64) sum_i double(y_i)/double(q_i)
+//     out_t = sum_i y_i * (Q_S/q_i mod p_t) - v * Q_S   (mod p_t)
+// The contraction over i is done with 128-bit multiply-accumulate against a Montgomery-form matrix and
+// one REDC per output, so the per-output cost is ns MACs + 2 wide multiplies.
+#include "kernels.h"
+
+namespace ob {
+
+namespace {
+
+constexpr int TPB = 256;
+constexpr int MAX_NS = 16;       // source limbs per conversion (digit size or #P)
+constexpr int DST_PER_CTA = 4;   // destination limbs handled by one CTA (y_i recomputed per CTA)
+
+template <bool CENTERED>
+__global__ void __launch_bounds__(TPB)
+baseconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, int ns, int nd,
+                const int* __restrict__ src_mod, const int* __restrict__ dst_mod, const LimbDesc* __restrict__ out_off,
+                const ulonglong2* __restrict__ inv, const u64* __restrict__ mat, const u64* __restrict__ negvq,
+                const u64* __restrict__ half_src, const u64* __restrict__ half_dst,
+                const ModConst* __restrict__ mc) {
+    const int x = blockIdx.x * TPB + threadIdx.x;
+    u64 y[MAX_NS];
+    double vf = 0.0;
+#pragma unroll
+    for (int i = 0; i < MAX_NS; ++i) {
+        if (i < ns) {
+            const ModConst& m = mc[src_mod[i]];
+            u64 xi = in[(size_t)i * N + x];
+            if (CENTERED) xi = add_mod(xi, half_src[i], m.q);
+            const ulonglong2 w = inv[i];
+            y[i] = shoup_mul(xi, w.x, w.y, m.q);
+            vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(y[i]), m.qd));
+        }
+    }
+    // a single source modulus without centring is a plain copy + reduction (v is 0 by definition)
+    const u64 v = (ns == 1 && !CENTERED) ? 0 : (u64)vf;
+    const int d0 = blockIdx.y * DST_PER_CTA;
+#pragma unroll
+    for (int dd = 0; dd < DST_PER_CTA; ++dd) {
+        const int d = d0 + dd;
+        if (d >= nd) break;
+        const ModConst m = mc[dst_mod[d]];
+        u64 hi = 0, lo = 0;
+#pragma unroll
+        for (int i = 0; i < MAX_NS; ++i)
+            if (i < ns) mac128(hi, lo, y[i], __ldg(&mat[(size_t)i * nd + d]), m.q);
+        u64 r = mont_redc(hi, lo, m.q, m.qinv_neg);
+        r = add_mod(r, __ldg(&negvq[(size_t)d * (ns + 1) + v]), m.q);
+        if (CENTERED) r = sub_mod(r, half_dst[d], m.q);
+        out[(size_t)out_off[d].in_off * N + x] = r;
+    }
+}
+
+// acc[c][t][x] (+)= sum_j dig_j[t][x] * evk[j][c][chain(t)][x]   (evk Montgomery form)
+template <bool GATHER, bool ACCUM>
+__global__ void __launch_bounds__(TPB)
+inner_product_kernel(const u64* __restrict__ c1, const u64* __restrict__ digits, const u64* __restrict__ evk,
+                     u64* __restrict__ acc, int N, int L, int K, int nQ, int nmod, int beta,
+                     const uint32_t* __restrict__ gather, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, W = L + K;
+    const int x = blockIdx.x * TPB + threadIdx.x;
+    const int ci = t < L ? t : nQ + (t - L);
+    const ModConst m = mc[ci];
+    const int own = t < L ? t / K : -1;
+    const int xs = GATHER ? (int)__ldg(&gather[x]) : x;
+    u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
+    for (int j = 0; j < beta; ++j) {
+        const u64 d = (j == own) ? c1[(size_t)t * N + xs] : digits[((size_t)j * W + t) * N + xs];
+        const u64 k0 = evk[(((size_t)j * 2 + 0) * nmod + ci) * N + x];
+        const u64 k1 = evk[(((size_t)j * 2 + 1) * nmod + ci) * N + x];
+        mac128(h0, l0, d, k0, m.q);
+        mac128(h1, l1, d, k1, m.q);
+    }
+    u64 r0 = mont_redc(h0, l0, m.q, m.qinv_neg), r1 = mont_redc(h1, l1, m.q, m.qinv_neg);
+    const size_t o0 = (size_t)t * N + x, o1 = ((size_t)W + t) * N + x;
+    if (ACCUM) { r0 = add_mod(r0, acc[o0], m.q); r1 = add_mod(r1, acc[o1], m.q); }
+    acc[o0] = r0; acc[o1] = r1;
+}
+
+__global__ void __launch_bounds__(TPB)
+moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __restrict__ conv, int L,
+                      const u64* __restrict__ addend, int addend_stride, int addend_polys,
+                      u64* __restrict__ out, int out_stride, int N,
+                      const ulonglong2* __restrict__ pinv, const ModConst* __restrict__ mc) {
+    const int i = blockIdx.y, p = blockIdx.z;
+    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
+    const u64 q = mc[i].q;
+    const ulonglong2 w = pinv[i];
+    const ulonglong2 a = *(const ulonglong2*)(acc + ((size_t)p * acc_stride + i) * N + x);
+    const ulonglong2 b = *(const ulonglong2*)(conv + ((size_t)p * L + i) * N + x);
+    ulonglong2 r;
+    r.x = shoup_mul(sub_mod(a.x, b.x, q), w.x, w.y, q);
+    r.y = shoup_mul(sub_mod(a.y, b.y, q), w.x, w.y, q);
+    if (addend != nullptr && p < addend_polys) {
+        const ulonglong2 e = *(const ulonglong2*)(addend + ((size_t)p * addend_stride + i) * N + x);
+        r.x = add_mod(r.x, e.x, q); r.y = add_mod(r.y, e.y, q);
+    }
+    *(ulonglong2*)(out + ((size_t)p * out_stride + i) * N + x) = r;
+}
+
+// tmp[p][i][x] = ((last[p][x] + (q_l-1)/2) mod q_l) mod q_i - ((q_l-1)/2 mod q_i)        (coefficient domain)
+__global__ void __launch_bounds__(TPB)
+rescale_prep_kernel(const u64* __restrict__ last, u64* __restrict__ tmp, int level, int N,
+                    const ModConst* __restrict__ mc) {
+    const int i = blockIdx.y, p = blockIdx.z;
+    const int x = blockIdx.x * TPB + threadIdx.x;
+    const u64 ql = mc[level].q, half = (ql - 1) >> 1;
+    const ModConst m = mc[i];
+    const u64 s = add_mod(last[(size_t)p * N + x], half, ql);
+    const u64 u = barrett_red(0, s, m), hq = barrett_red(0, half, m);
+    tmp[((size_t)p * level + i) * N + x] = sub_mod(u, hq, m.q);
+}
+// out[p][i][x] = (in[p][i][x] - tmp[p][i][x]) * q_l^-1 mod q_i
+__global__ void __launch_bounds__(TPB)
+rescale_finish_kernel(const u64* __restrict__ in, int in_stride, const u64* __restrict__ tmp,
+                      u64* __restrict__ out, int out_stride, int level, int N,
+                      const ulonglong2* __restrict__ qlinv_row, const ModConst* __restrict__ mc) {
+    const int i = blockIdx.y, p = blockIdx.z;
+    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
+    const u64 q = mc[i].q;
+    const ulonglong2 w = qlinv_row[i];
+    const ulonglong2 a = *(const ulonglong2*)(in + ((size_t)p * in_stride + i) * N + x);
+    const ulonglong2 b = *(const ulonglong2*)(tmp + ((size_t)p * level + i) * N + x);
+    ulonglong2 r;
+    r.x = shoup_mul(sub_mod(a.x, b.x, q), w.x, w.y, q);
+    r.y = shoup_mul(sub_mod(a.y, b.y, q), w.x, w.y, q);
+    *(ulonglong2*)(out + ((size_t)p * out_stride + i) * N + x) = r;
+}
+
+}  // namespace
+
+BaseConvPlan make_baseconv_plan(Context& c, const std::vector<int>& src, const std::vector<int>& dst,
+                                const std::vector<int>& out_off) {
+    OB_CHECK((int)src.size() <= MAX_NS, "too many source limbs for one base conversion");
+    OB_CHECK(dst.size() == out_off.size(), "out_off size");
+    BaseConvPlan p;
+    p.bc = &c.base_conv(src, dst);
+    std::vector<LimbDesc> tmp(out_off.size());            // destination offsets ride in LimbDesc::in_off
+    for (size_t i = 0; i < out_off.size(); ++i) tmp[i] = LimbDesc{(uint32_t)out_off[i], 0u, 0u, 0xB0C0u};
+    p.out_off = c.limb_list(tmp);
+    return p;
+}
+
+void base_convert(Context& c, const BaseConvPlan& p, const u64* in, u64* out, bool centered) {
+    const BaseConv& b = *p.bc;
+    dim3 grid(c.N / TPB, (b.nd + DST_PER_CTA - 1) / DST_PER_CTA);
+    if (centered)
+        OB_LAUNCH((baseconv_kernel<true>), grid, TPB, 0, stream(), in, out, c.N, b.ns, b.nd, b.src_mod.as<int>(),
+                  b.dst_mod.as<int>(), p.out_off, b.inv.as<ulonglong2>(), b.mat.u(), b.negvq.u(), b.half_src.u(),
+                  b.half_dst.u(), c.dmc());
+    else
+        OB_LAUNCH((baseconv_kernel<false>), grid, TPB, 0, stream(), in, out, c.N, b.ns, b.nd, b.src_mod.as<int>(),
+                  b.dst_mod.as<int>(), p.out_off, b.inv.as<ulonglong2>(), b.mat.u(), b.negvq.u(), b.half_src.u(),
+                  b.half_dst.u(), c.dmc());
+}
+
+void ks_inner_product(Context& c, int level, const u64* c1_ntt, const u64* digits, const u64* evk,
+                      u64* acc, const uint32_t* gather, bool accumulate) {
+    const int L = level + 1, K = c.nP, W = L + K, beta = c.num_digits(level);
+    dim3 grid(c.N / TPB, W);
+#define OB_IP(G, A) OB_LAUNCH((inner_product_kernel<G, A>), grid, TPB, 0, stream(), c1_ntt, digits, evk, acc, c.N, \
+                              L, K, c.nQ, c.nmod, beta, gather, c.dmc())
+    if (gather) { if (accumulate) OB_IP(true, true); else OB_IP(true, false); }
+    else        { if (accumulate) OB_IP(false, true); else OB_IP(false, false); }
+#undef OB_IP
+}
+
+void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
+                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys) {
+    dim3 grid(c.N / (2 * TPB), level + 1, polys);
+    OB_LAUNCH(moddown_finish_kernel, grid, TPB, 0, stream(), acc, acc_stride, conv, level + 1, addend, addend_stride,
+              addend_polys, out, out_stride, c.N, c.d_pinv.as<ulonglong2>(), c.dmc());
+}
+
+void rescale_prep(Context& c, int level, const u64* last_coeff, u64* tmp, int polys) {
+    dim3 grid(c.N / TPB, level, polys);
+    OB_LAUNCH(rescale_prep_kernel, grid, TPB, 0, stream(), last_coeff, tmp, level, c.N, c.dmc());
+}
+void rescale_finish(Context& c, int level, const u64* in, int in_stride, const u64* tmp, u64* out, int out_stride, int polys) {
+    dim3 grid(c.N / (2 * TPB), level, polys);
+    OB_LAUNCH(rescale_finish_kernel, grid, TPB, 0, stream(), in, in_stride, tmp, out, out_stride, level, c.N,
+              c.d_qlinv.as<ulonglong2>() + (size_t)level * c.nQ, c.dmc());
+}
+
+}  // namespace ob

@@ -1,0 +1,114 @@
+"""GPU parity of the hot-path primitives against the CPU oracle, through the C ABI (B200_*).  Bit-exact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CASES = [  # (logN, LogQ, LogP)
+    (12, [40, 30, 30, 30], [40, 40]),
+    (13, [29, 26, 26, 26, 26, 26], [29, 29]),          # configs/mlp.yml
+    (14, [60, 30, 30, 30, 30, 30, 30], [60, 60]),      # configs/lola2.yml
+    (13, [55, 40, 40, 40, 40, 40, 40], [61, 61, 61]),  # partial last digit (7 = 3+3+1)
+]
+
+
+def make(orc, b200lib, case):
+    logN, lq, lp = case
+    Q, P = orc.gen_moduli(lq, lp, logN + 1)
+    Qg, Pg = b200lib.gen_moduli(lq, lp, logN + 1)
+    assert (Q, P) == (Qg, Pg), "prime selection differs between library and oracle"
+    oc = orc.Ctx(logN, Q + P, len(Q), len(P))
+    gc = b200lib.RawContext(logN, Q, P)
+    for i in range(len(Q) + len(P)):
+        assert gc.psi(i) == int(oc.L.orc_ctx_psi(oc.h, i))
+    return oc, gc
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_ntt_roundtrip_and_parity(orc, b200lib, case):
+    oc, gc = make(orc, b200lib, case)
+    rng = np.random.default_rng(7)
+    idx = list(range(oc.nQ + oc.nP))
+    a = oc.uniform_poly(rng, idx)
+    f = gc.ntt(a, idx)
+    assert np.array_equal(f, oc.ntt(a, idx))
+    b = gc.ntt(f, idx, inverse=True)
+    assert np.array_equal(b, a)
+    assert np.array_equal(gc.ntt(a, idx, inverse=True), oc.ntt(a, idx, inverse=True))
+    # edge values: 0, q-1
+    e = np.stack([np.full(oc.N, oc.moduli[m] - 1, dtype=np.uint64) for m in idx])
+    assert np.array_equal(gc.ntt(e, idx), oc.ntt(e, idx))
+    z = np.zeros_like(e)
+    assert np.array_equal(gc.ntt(z, idx), z)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_baseconv(orc, b200lib, case):
+    oc, gc = make(orc, b200lib, case)
+    rng = np.random.default_rng(8)
+    K = oc.nP
+    src = list(range(0, min(K, oc.nQ)))
+    dst = [i for i in range(oc.nQ + K) if i not in src]
+    a = oc.uniform_poly(rng, src)
+    assert np.array_equal(gc.baseconv(a, src, dst), oc.baseconv(a, src, dst))
+    psrc = list(range(oc.nQ, oc.nQ + K))
+    qdst = list(range(oc.nQ))
+    b = oc.uniform_poly(rng, psrc)
+    assert np.array_equal(gc.baseconv(b, psrc, qdst, centered=True), oc.baseconv(b, psrc, qdst, centered=True))
+    # single source limb: copy + reduce
+    c = oc.uniform_poly(rng, [0])
+    assert np.array_equal(gc.baseconv(c, [0], dst), oc.baseconv(c, [0], dst))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_elementwise_and_automorphism(orc, b200lib, case):
+    oc, gc = make(orc, b200lib, case)
+    rng = np.random.default_rng(9)
+    idx = list(range(oc.nQ))
+    a, b = oc.uniform_poly(rng, idx), oc.uniform_poly(rng, idx)
+    for op in ("add", "sub", "mul"):
+        assert np.array_equal(gc.elementwise(op, a, b), oc.elementwise(op, a, b)), op
+    assert np.array_equal(gc.elementwise("neg", a), oc.elementwise("neg", a))
+    for rot in (1, 5, -3, oc.N // 4):
+        g = oc.galois_element(rot)
+        assert g == gc.galois_element(rot)
+        assert np.array_equal(gc.automorphism_ntt(a, g), oc.automorphism_ntt(a, g))
+    g = 2 * oc.N - 1
+    assert np.array_equal(gc.automorphism_ntt(a, g), oc.automorphism_ntt(a, g))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_rescale(orc, b200lib, case):
+    oc, gc = make(orc, b200lib, case)
+    rng = np.random.default_rng(10)
+    for level in (oc.nQ - 1, 1):
+        a = oc.uniform_poly(rng, list(range(level + 1)))
+        b = oc.uniform_poly(rng, list(range(level + 1)))
+        out = gc.rescale(level, np.stack([a, b]), polys=2)
+        assert np.array_equal(out[0], oc.rescale(level, a))
+        assert np.array_equal(out[1], oc.rescale(level, b))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_keyswitch_stages_and_full(orc, b200lib, case):
+    oc, gc = make(orc, b200lib, case)
+    rng = np.random.default_rng(11)
+    nmod = oc.nQ + oc.nP
+    beta_max = oc.num_digits(oc.nQ - 1)
+    evk = np.stack([oc.uniform_poly(rng, list(range(nmod))) for _ in range(beta_max * 2)]).reshape(beta_max, 2, nmod, oc.N)
+    evk_dev = gc.evk_to_device(evk)
+    for level in sorted({oc.nQ - 1, max(0, oc.nQ - 2), 0}):
+        c1 = oc.uniform_poly(rng, list(range(level + 1)))
+        c0 = oc.uniform_poly(rng, list(range(level + 1)))
+        dg = gc.decompose(level, c1)
+        assert np.array_equal(dg, oc.decompose(level, c1)), "decompose level %d" % level
+        acc = oc.uniform_poly(rng, list(range(level + 1)) + list(range(oc.nQ, nmod)))
+        assert np.array_equal(gc.moddown(level, acc), oc.moddown(level, acc)), "moddown level %d" % level
+        ref = oc.keyswitch(level, c1, evk)
+        out = gc.keyswitch(level, c1, evk_dev)
+        assert np.array_equal(out, ref), "keyswitch level %d" % level
+        out2 = gc.keyswitch(level, c1, evk_dev, c0=c0)
+        ref2 = ref.copy()
+        ref2[0] = oc.elementwise("add", ref[0], c0)
+        assert np.array_equal(out2, ref2)
+    gc.lib.B200_DevFree(evk_dev)
