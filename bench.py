@@ -1,0 +1,277 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 CKKS backend (contract: see the task statement / DESIGN.md).
+
+Metric (BASELINE.json): key switches per second at logN=16.  One step = one batch of independent hybrid key
+switches (the unit of work inside rotation, relinearisation, every BSGS step and every bootstrap DFT layer) at
+logN=16, L=24 Q-limbs, k=3 special primes (beta=8 digits) -- the upper end of BASELINE.json's primitive sweep.
+Ciphertexts are sharded across ranks (no data-path collective): weak scaling.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LOGN = 16
+LOGQ = [60] + [45] * 23          # 24 Q-limbs
+LOGP = [61, 61, 61]              # 3 special primes -> beta = 8
+BATCH = 8                        # key switches per step per GPU
+N_EVK = 4                        # distinct evaluation keys cycled through (4 x 216 MB >> 126 MB L2)
+METRIC = "keyswitches_per_s_logN16"
+UNIT = "keyswitch/s"
+
+
+def workload_name():
+    return "hybrid key switch, logN=16, L=24 Q-limbs (60+23x45 bit), k=3 P-limbs (61 bit), beta=8, batch %d/GPU" % BATCH
+
+
+def algorithmic_bytes_keyswitch(N, L, K):
+    beta = (L + K - 1) // K
+    return 8 * N * (4 * L + 2 * beta * (L + K))          # ct in + evk + ct out
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name).read().strip().splitlines() if r.strip()]
+        os.unlink(self.f.name)
+        sm, reasons = [], set()
+        for r in rows:
+            try:
+                sm.append(float(r[0])); out["sm_max_mhz"] = float(r[1])
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.strip().lower() == "active":
+                    reasons.add(name)
+        if sm:
+            out["sm_mhz"] = statistics.median(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def cpu_keyswitch_rate(threads, budget_s=12.0):
+    """Oracle (CPU restatement, OpenMP) timed on the same workload: a bounded sample of whole key switches."""
+    import oracle
+    Q, P = oracle.gen_moduli(LOGQ, LOGP, LOGN + 1)
+    oc = oracle.Ctx(LOGN, Q + P, len(Q), len(P))
+    oc.L.orc_set_threads(threads)
+    rng = np.random.default_rng(1234)
+    level = len(Q) - 1
+    nmod = len(Q) + len(P)
+    beta = oc.num_digits(level)
+    evk = rng.integers(0, 1 << 44, size=(beta, 2, nmod, oc.N), dtype=np.uint64)
+    c1 = oc.uniform_poly(rng, list(range(level + 1)))
+    oc.keyswitch(level, c1, evk)                      # warm-up (page faults, table caches)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        oc.keyswitch(level, c1, evk)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > budget_s or n >= 64:
+            break
+    return n / dt, n, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    steps_total = max(1, args.steps)
+    rate, n, dt = cpu_keyswitch_rate(threads, budget_s=min(60.0, 4.0 * steps_total))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1000.0 * dt / n, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": workload_name(), "note": "CPU oracle (C restatement of the Lattigo algorithm, OpenMP); "
+                   "Lattigo itself cannot be built here (no Go toolchain, module not vendored)"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "%d whole key switches at logN=16, L=24, k=3 in %.1f s" % (n, dt)},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    os.environ.setdefault("ORION_B200_DEVICE", str(local))
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    from orion_b200 import raw
+    lib = raw.load()
+    Q, P = raw.gen_moduli(LOGQ, LOGP, LOGN + 1)
+    ctx = raw.RawContext(LOGN, Q, P)
+    N, L, K = ctx.N, len(Q), len(P)
+    level, nmod, beta = L - 1, L + K, ctx.num_digits(L - 1)
+    LN = L * N
+    rng = np.random.default_rng(1234 + rank)
+
+    # synthetic operands: limbs uniform below 2^44 (< every modulus), seeded -- values do not affect timing
+    evks = []
+    for e in range(N_EVK):
+        h = rng.integers(0, 1 << 44, size=beta * 2 * nmod * N, dtype=np.uint64)
+        evks.append(ctx.evk_to_device(h))
+        del h
+    host_in = [np.ctypeslib.as_array(ctypes_cast(lib.B200_HostAllocPinned(2 * LN), 2 * LN)) for _ in range(BATCH)]
+    host_out = [np.ctypeslib.as_array(ctypes_cast(lib.B200_HostAllocPinned(2 * LN), 2 * LN)) for _ in range(BATCH)]
+    for b in range(BATCH):
+        host_in[b][:] = rng.integers(0, 1 << 44, size=2 * LN, dtype=np.uint64)
+    dev_in = [lib.B200_DevAlloc(2 * LN) for _ in range(BATCH)]
+    dev_out = [lib.B200_DevAlloc(2 * LN) for _ in range(BATCH)]
+    for b in range(BATCH):
+        lib.B200_Upload(dev_in[b], raw._p(host_in[b]), 2 * LN)
+
+    def step_resident(s):
+        for b in range(BATCH):
+            lib.B200_KeySwitchDev(ctx.h, level, dev_in[b] + LN * 8, evks[(s * BATCH + b) % N_EVK], dev_in[b], dev_out[b])
+
+    def step_e2e(s):
+        for b in range(BATCH):
+            lib.B200_UploadAsync(dev_in[b], raw._p(host_in[b]), 2 * LN)
+            lib.B200_KeySwitchDev(ctx.h, level, dev_in[b] + LN * 8, evks[(s * BATCH + b) % N_EVK], dev_in[b], dev_out[b])
+            lib.B200_Download(raw._p(host_out[b]), dev_out[b], 2 * LN)
+
+    def barrier():
+        lib.B200_Sync(); torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        lib.B200_Sync(); torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        l0 = lib.B200_LaunchCount()
+        lib.B200_TimerStart()
+        for s in range(steps):
+            fn(s)
+        ms = lib.B200_TimerStopMs()
+        launches = lib.B200_LaunchCount() - l0
+        barrier()
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches
+
+    for s in range(args.warmup):
+        step_resident(s)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, launches = timed(step_resident, args.steps)
+    clocks = sampler.stop() if sampler else None
+    for s in range(max(1, args.warmup // 2)):
+        step_e2e(s)
+    e2e_steps = max(2, args.steps // 4)
+    ms_e2e, _ = timed(step_e2e, e2e_steps)
+
+    # roofline of the dominant kernel class: the batched NTT over the converted digit limbs (beta*W - L limbs),
+    # timed alone with CUDA events on the library stream, inputs 99 MB per launch pair cycled over > L2
+    nl = beta * nmod - L
+    mods = [(i % nmod) for i in range(nl)]
+    big = [lib.B200_DevAlloc(nl * N) for _ in range(3)]            # 3 x 100 MB working sets
+    midx = raw._ints(mods)
+    reps = 12
+    lib.B200_Sync()
+    for i in range(3):
+        lib.B200_NTTDev(ctx.h, big[i], big[i], midx, nl, 0)
+    lib.B200_Sync()
+    lib.B200_TimerStart()
+    for i in range(reps):
+        lib.B200_NTTDev(ctx.h, big[i % 3], big[i % 3], midx, nl, 0)
+    ntt_ms = lib.B200_TimerStopMs() / reps
+    ntt_bytes = 2 * 16 * N * nl                                       # two passes, each reads + writes every limb
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    ntt_gbs = ntt_bytes / (ntt_ms * 1e-3) / 1e9
+
+    total_ks = BATCH * args.steps * world
+    value = total_ks / (ms * 1e-3)
+    e2e_value = BATCH * e2e_steps * world / (ms_e2e * 1e-3)
+    ks_bytes = algorithmic_bytes_keyswitch(N, L, K)
+
+    if rank == 0:
+        cpu = None
+        if not args.no_cpu_baseline and world == 1:
+            threads = os.cpu_count() or 1
+            rate, n, dt = cpu_keyswitch_rate(threads)
+            cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": "%d whole key switches at logN=16, L=24, k=3 in %.1f s (oracle, OpenMP)" % (n, dt)}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(), "l2": "inputs larger than L2: %d evaluation keys x 216 MB cycled" % N_EVK,
+                       "keyswitch_algorithmic_bytes": ks_bytes,
+                       "keyswitch_hbm_floor_frac": (ks_bytes * total_ks / (ms * 1e-3) / 1e9 / world) / peak},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * 2 * LN * 8,
+                    "d2h_bytes_per_step": BATCH * 2 * LN * 8},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "ntt_pass (forward NTT of the %d converted digit limbs, 2 launches)" % nl,
+                         "achieved": ntt_gbs, "peak": peak, "unit": "GB/s", "frac": ntt_gbs / peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                         "traffic": None},
+            "clocks": clocks,
+        }
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ctypes_cast(ptr, words):
+    import ctypes
+    return ctypes.cast(ptr, ctypes.POINTER(ctypes.c_uint64 * words)).contents
+
+
+if __name__ == "__main__":
+    main()
