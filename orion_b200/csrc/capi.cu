@@ -1,0 +1,326 @@
+// capi.cu -- the Orion-facing C ABI: the export names, argument order and conventions of the Go shim
+// orion/backend/lattigo/*.go (bound by orion/backend/lattigo/bindings.py:126-746), backed by the device-resident
+// Scheme.  One process-global scheme, integer handles from smallest-free-int tables, arrays returned by value as
+// {Data, Length} and released with FreeCArray, abort on error -- all as in the reference.
+// Declarations with per-function reference citations: include/orion_b200_scheme.h.
+#include "scheme.h"
+#include "lintrans.h"
+#include "../../include/orion_b200_scheme.h"
+#include <cmath>
+#include <random>
+
+using namespace ob;
+
+namespace ob {
+std::unique_ptr<Scheme> g_scheme;
+static u64 g_seed = 0;
+static bool g_seed_set = false;
+Scheme& S() {
+    if (!g_scheme) OB_FATAL("no scheme: call NewScheme first");
+    return *g_scheme;
+}
+}  // namespace ob
+
+namespace {
+template <class T, class A> A make_array(const std::vector<T>& v) {
+    A a;
+    a.Length = (unsigned long)v.size();
+    a.Data = (decltype(a.Data))std::malloc(std::max<size_t>(1, v.size()) * sizeof(*a.Data));
+    for (size_t i = 0; i < v.size(); ++i) a.Data[i] = (std::remove_pointer_t<decltype(a.Data)>)v[i];
+    return a;
+}
+int push_ct(std::unique_ptr<Ciphertext> c) { return S().cts.add(std::move(c)); }
+int push_pt(std::unique_ptr<Plaintext> p) { return S().pts.add(std::move(p)); }
+Ciphertext& CT(int id) { return S().cts.get(id, "ciphertext"); }
+Plaintext& PT(int id) { return S().pts.get(id, "plaintext"); }
+std::unique_ptr<Ciphertext> fresh() { return std::make_unique<Ciphertext>(); }
+}  // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------- scheme
+void B200_SetSeed(uint64_t seed) { g_seed = seed; g_seed_set = true; }
+
+void NewScheme(int logN, int* logQ, int lenQ, int* logP, int lenP, int logScale, int h, char* ringType, char* keysPath, char* ioMode) {
+    (void)keysPath; (void)ioMode;
+    SchemeParams p;
+    p.logN = logN; p.log_scale = logScale; p.h = h;
+    p.logQ.assign(logQ, logQ + lenQ); p.logP.assign(logP, logP + lenP);
+    std::string rt = ringType ? ringType : "standard";
+    for (auto& ch : rt) ch = (char)std::tolower(ch);
+    p.conjugate_invariant = (rt != "standard");
+    u64 seed = g_seed;
+    if (!g_seed_set) { std::random_device rd; seed = ((u64)rd() << 32) ^ rd(); }   // OS randomness, as Lattigo does
+    lt_reset();
+    g_scheme.reset();
+    g_scheme = std::make_unique<Scheme>(p, seed);
+}
+void DeleteScheme(void) {
+    lt_reset();
+    g_scheme.reset();
+}
+void FreeCArray(void* p) { std::free(p); }
+
+// ---------------------------------------------------------------- tensors
+void DeletePlaintext(int id) { S().pts.del(id); }
+void DeleteCiphertext(int id) { S().cts.del(id); }
+unsigned long GetPlaintextScale(int id) { return (unsigned long)PT(id).scale; }
+unsigned long GetCiphertextScale(int id) { return (unsigned long)CT(id).scale; }
+void SetPlaintextScale(int id, unsigned long scale) { PT(id).scale = (scale_t)scale; }
+void SetCiphertextScale(int id, unsigned long scale) { CT(id).scale = (scale_t)scale; }
+int GetPlaintextLevel(int id) { return PT(id).level; }
+int GetCiphertextLevel(long id) { return CT((int)id).level; }
+int GetPlaintextSlots(long id) { return 1 << PT((int)id).log_slots; }
+int GetCiphertextSlots(long id) { return 1 << CT((int)id).log_slots; }
+int GetCiphertextDegree(long id) { return CT((int)id).degree; }
+ArrayResultUInt64 GetModuliChain(void) {
+    std::vector<u64> q(S().ctx->mod.begin(), S().ctx->mod.begin() + S().nQ);
+    return make_array<u64, ArrayResultUInt64>(q);
+}
+ArrayResultInt GetLivePlaintexts(void) { return make_array<int, ArrayResultInt>(S().pts.ids()); }
+ArrayResultInt GetLiveCiphertexts(void) { return make_array<int, ArrayResultInt>(S().cts.ids()); }
+
+// ---------------------------------------------------------------- key generator
+void NewKeyGenerator(void) { S(); }
+void GenerateSecretKey(void) { S().gen_secret_key(); }
+void GeneratePublicKey(void) { S().gen_public_key(); }
+void GenerateRelinearizationKey(void) { S().gen_relin_key(); }
+void GenerateEvaluationKeys(void) { S(); }     // the reference only wraps the relin key in an (empty) key set here
+ArrayResultByte SerializeSecretKey(void) {
+    // own container, not Lattigo's MarshalBinary: "OB2SK1\0\0" | u64 N | N x int8 ternary coefficients
+    Scheme& s = S();
+    OB_CHECK(s.has_sk(), "no secret key to serialize");
+    std::vector<unsigned char> b(16 + s.N);
+    std::memcpy(b.data(), "OB2SK1\0\0", 8);
+    u64 n = s.N; std::memcpy(b.data() + 8, &n, 8);
+    for (int i = 0; i < s.N; ++i) b[16 + i] = (unsigned char)(signed char)s.sk_coeffs[i];
+    return make_array<unsigned char, ArrayResultByte>(b);
+}
+void LoadSecretKey(unsigned char* data, unsigned long len) {
+    Scheme& s = S();
+    OB_CHECK(len == (unsigned long)(16 + s.N) && std::memcmp(data, "OB2SK1\0\0", 8) == 0, "LoadSecretKey: not an orion_b200 secret key blob");
+    std::vector<int64_t> c(s.N);
+    for (int i = 0; i < s.N; ++i) c[i] = (int64_t)(signed char)data[16 + i];
+    s.set_secret_key(c);
+}
+
+// ---------------------------------------------------------------- encoder / encryptor
+void NewEncoder(void) { S(); }
+int Encode(float* values, int lenValues, int level, unsigned long scale) {
+    Scheme& s = S();
+    std::vector<double> v(values, values + lenValues);
+    return push_pt(s.encode(v.data(), lenValues, level, (scale_t)scale, s.log_max_slots));
+}
+ArrayResultFloat Decode(int ptID) {
+    std::vector<double2> v = S().decode(PT(ptID));
+    std::vector<float> out(1 << S().log_max_slots, 0.0f);
+    for (size_t i = 0; i < v.size() && i < out.size(); ++i) out[i] = (float)v[i].x;
+    return make_array<float, ArrayResultFloat>(out);
+}
+void NewEncryptor(void) { S(); }
+void NewDecryptor(void) { S(); }
+int Encrypt(int ptID) { return push_ct(S().encrypt(PT(ptID))); }
+int Decrypt(int ctID) { return push_pt(S().decrypt(CT(ctID))); }
+
+// ---------------------------------------------------------------- evaluator
+void B200_NoteEvaluatorKey(uint64_t g);
+void AddRotationKey(int rot) { u64 g = S().ctx->galois_element(rot); B200_NoteEvaluatorKey(g); S().galois_key(g); }
+void NewEvaluator(void) {
+    Scheme& s = S();
+    if (!s.has_sk()) return;
+    for (int i = 1; i < (1 << s.log_max_slots); i *= 2) AddRotationKey(i);                        // LG/evaluator.go:25-31
+}
+int Negate(int ct) { auto o = fresh(); S().mul_int(CT(ct), -1, *o); return push_ct(std::move(o)); }
+int Rotate(int ct, int rot) { AddRotationKey(rot); S().rotate(CT(ct), rot, CT(ct)); return ct; }
+int RotateNew(int ct, int rot) { AddRotationKey(rot); auto o = fresh(); S().rotate(CT(ct), rot, *o); return push_ct(std::move(o)); }
+int Rescale(int ct) { S().rescale(CT(ct), CT(ct)); return ct; }
+int RescaleNew(int ct) { S().rescale(CT(ct), CT(ct)); return push_ct(S().clone(CT(ct))); }   // LG/evaluator.go:91-99: rescales the input too
+int AddScalar(int ct, float c) { S().add_const(CT(ct), (double)c, CT(ct)); return ct; }
+int AddScalarNew(int ct, float c) { auto o = fresh(); S().add_const(CT(ct), (double)c, *o); return push_ct(std::move(o)); }
+int SubScalar(int ct, float c) { S().add_const(CT(ct), -(double)c, CT(ct)); return ct; }
+int SubScalarNew(int ct, float c) { auto o = fresh(); S().add_const(CT(ct), -(double)c, *o); return push_ct(std::move(o)); }
+int MulScalarInt(int ct, int k) { S().mul_int(CT(ct), k, CT(ct)); return ct; }
+int MulScalarIntNew(int ct, int k) { auto o = fresh(); S().mul_int(CT(ct), k, *o); return push_ct(std::move(o)); }
+int MulScalarFloat(int ct, float c) { S().mul_float(CT(ct), (double)c, CT(ct)); return ct; }
+int MulScalarFloatNew(int ct, float c) { auto o = fresh(); S().mul_float(CT(ct), (double)c, *o); return push_ct(std::move(o)); }
+int AddPlaintext(int ct, int pt) { S().add_pt(CT(ct), PT(pt), CT(ct), false); return ct; }
+int AddPlaintextNew(int ct, int pt) { auto o = fresh(); S().add_pt(CT(ct), PT(pt), *o, false); return push_ct(std::move(o)); }
+int SubPlaintext(int ct, int pt) { S().add_pt(CT(ct), PT(pt), CT(ct), true); return ct; }
+int SubPlaintextNew(int ct, int pt) { auto o = fresh(); S().add_pt(CT(ct), PT(pt), *o, true); return push_ct(std::move(o)); }
+int MulPlaintext(int ct, int pt) { S().mul_pt(CT(ct), PT(pt), CT(ct)); return ct; }
+int MulPlaintextNew(int ct, int pt) { auto o = fresh(); S().mul_pt(CT(ct), PT(pt), *o); return push_ct(std::move(o)); }
+int AddCiphertext(int a, int b) { S().add_ct(CT(a), CT(b), CT(a), false); return a; }
+int AddCiphertextNew(int a, int b) { auto o = fresh(); S().add_ct(CT(a), CT(b), *o, false); return push_ct(std::move(o)); }
+int SubCiphertext(int a, int b) { S().add_ct(CT(a), CT(b), CT(a), true); return a; }
+int SubCiphertextNew(int a, int b) { auto o = fresh(); S().add_ct(CT(a), CT(b), *o, true); return push_ct(std::move(o)); }
+int MulRelinCiphertext(int a, int b) { S().mul_relin(CT(a), CT(b), CT(a)); return a; }
+int MulRelinCiphertextNew(int a, int b) { auto o = fresh(); S().mul_relin(CT(a), CT(b), *o); return push_ct(std::move(o)); }
+
+// ---------------------------------------------------------------- extras required by the (drifted) Python layer
+int CloneCiphertext(int ct) { return push_ct(S().clone(CT(ct))); }                    // PY/tensors.py:229
+int ModDropCiphertext(int ct) { Ciphertext& c = CT(ct); OB_CHECK(c.level >= 1, "mod drop at level 0"); S().drop_level(c, c.level - 1); return ct; }  // PY/evaluator.py:36-40
+
+// ---------------------------------------------------------------- interop: raw limbs in / out (parity tests, e2e bench, multi-GPU gather)
+int B200_ImportCiphertext(const uint64_t* data, int level, int degree, double scale, int logSlots) {
+    Scheme& s = S();
+    auto c = s.new_ct(level, degree, (scale_t)scale, logSlots > 0 ? logSlots : s.log_max_slots);
+    OB_CUDA(cudaMemcpyAsync(c->data.p, data, c->data.bytes, cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    return push_ct(std::move(c));
+}
+void B200_ExportCiphertext(int ct, uint64_t* out) {
+    Ciphertext& c = CT(ct);
+    OB_CUDA(cudaMemcpyAsync(out, c.data.p, (size_t)(c.degree + 1) * (c.level + 1) * S().N * 8, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+}
+void* B200_CiphertextDevicePtr(int ct) { return CT(ct).data.p; }
+double B200_GetCiphertextScaleF64(int ct) { return (double)CT(ct).scale; }
+void B200_SetCiphertextScaleF64(int ct, double s) { CT(ct).scale = (scale_t)s; }
+void B200_ExportPlaintext(int pt, uint64_t* out) {
+    Plaintext& p = PT(pt);
+    OB_CUDA(cudaMemcpyAsync(out, p.data.p, (size_t)(p.level + 1) * S().N * 8, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+}
+int B200_ImportPlaintext(const uint64_t* data, int level, double scale) {
+    Scheme& s = S();
+    auto p = std::make_unique<Plaintext>();
+    p->level = level; p->scale = (scale_t)scale; p->log_slots = s.log_max_slots;
+    p->data.alloc((size_t)(level + 1) * s.N * 8);
+    OB_CUDA(cudaMemcpyAsync(p->data.p, data, p->data.bytes, cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    return push_pt(std::move(p));
+}
+void B200_ExportSecretKey(int64_t* coeffs) { std::memcpy(coeffs, S().sk_coeffs.data(), (size_t)S().N * 8); }
+void B200_ImportSecretKey(const int64_t* coeffs) { S().set_secret_key(std::vector<int64_t>(coeffs, coeffs + S().N)); }
+// evaluation key in standard (non-Montgomery) residues: [beta][2][nQ+nP][N].  which: 0 = relin, else Galois element
+static void export_evk(const EvalKey& k, uint64_t* out) {
+    Scheme& s = S();
+    const int beta = s.ctx->num_digits(s.max_level), nmod = s.ctx->nmod;
+    DevBuf tmp(k.data.bytes);
+    from_montgomery(*s.ctx, k.data.u(), tmp.u(), beta * 2, nmod, s.nQ);
+    OB_CUDA(cudaMemcpyAsync(out, tmp.p, tmp.bytes, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+}
+void B200_ExportRelinKey(uint64_t* out) { OB_CHECK(S().rlk != nullptr, "no relin key"); export_evk(*S().rlk, out); }
+void B200_ExportGaloisKey(uint64_t galEl, uint64_t* out) { export_evk(S().galois_key(galEl), out); }
+void B200_ExportPublicKey(uint64_t* out) {
+    Scheme& s = S();
+    OB_CUDA(cudaMemcpyAsync(out, s.pk.p, s.pk.bytes, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+}
+int B200_SchemeInfo(int* logN, int* nQ, int* nP, uint64_t* moduli /* nQ+nP, may be NULL */) {
+    Scheme& s = S();
+    *logN = s.ctx->logN; *nQ = s.nQ; *nP = s.nP;
+    if (moduli) for (int i = 0; i < s.ctx->nmod; ++i) moduli[i] = s.ctx->mod[i];
+    return 0;
+}
+int B200_EncodeF64(const double* values, int n, int level, double scale) {
+    Scheme& s = S();
+    return push_pt(s.encode(values, n, level, (scale_t)scale, s.log_max_slots));
+}
+void B200_DecodeF64(int pt, double* out_re, double* out_im) {
+    std::vector<double2> v = S().decode(PT(pt));
+    for (size_t i = 0; i < v.size(); ++i) { out_re[i] = v[i].x; if (out_im) out_im[i] = v[i].y; }
+}
+int B200_Conjugate(int ct) { auto o = fresh(); S().conjugate(CT(ct), *o); return push_ct(std::move(o)); }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- linear transforms (LG/lineartransform.go:26-211)
+namespace {
+std::set<u64> g_eval_keys;      // Galois elements owned by the evaluator (power-of-two rotations, AddRotationKey)
+std::set<u64> g_lt_keys;        // Galois elements generated for linear transforms (dropped by RemoveRotationKeys)
+}
+extern "C" {
+
+void B200_NoteEvaluatorKey(uint64_t g) { g_eval_keys.insert(g); }
+void NewLinearTransformEvaluator(void) { S(); }
+
+int GenerateLinearTransform(int* diagIdx, int nIdx, float* diagData, int nData, int level, float bsgsRatio, char* ioMode) {
+    Scheme& s = S();
+    const int slots = 1 << s.log_max_slots;
+    OB_CHECK((long long)nData == (long long)nIdx * slots, "GenerateLinearTransform: diagData must hold nIdx * slots values");
+    std::map<int, std::vector<double2>> diags;
+    for (int k = 0; k < nIdx; ++k) {
+        std::vector<double2>& v = diags[diagIdx[k]];
+        v.resize(slots);
+        for (int x = 0; x < slots; ++x) v[x] = make_double2((double)diagData[(size_t)k * slots + x], 0.0);
+    }
+    const int log_ratio = (int)std::log((double)bsgsRatio);      // natural log, as LG/lineartransform.go:67
+    (void)ioMode;   // "load" is served by LoadPlaintextDiagonal overwriting the encoded diagonals
+    return lt_push(lt_build(s, diags, level, s.q_at(level), s.log_max_slots, log_ratio));
+}
+int EvaluateLinearTransform(int transform, int ct) { return push_ct(lt_apply(S(), lt_get(transform), CT(ct))); }
+void DeleteLinearTransform(int id) { lt_delete(id); }
+ArrayResultInt GetLinearTransformRotationKeys(int transform) {
+    return make_array<u64, ArrayResultInt>(lt_galois_elements(S(), lt_get(transform)));
+}
+void GenerateLinearTransformRotationKey(int galEl) {
+    if (!S().has_galois_key((u64)galEl)) g_lt_keys.insert((u64)galEl);
+    S().galois_key((u64)galEl);
+}
+// own containers (not Lattigo MarshalBinary): "OB2GK1\0\0" | u64 galEl | u64 words | data (Montgomery form)
+ArrayResultByte GenerateAndSerializeRotationKey(int galEl) {
+    Scheme& s = S();
+    const bool had = s.has_galois_key((u64)galEl);
+    const EvalKey& k = s.galois_key((u64)galEl);
+    ArrayResultByte a;
+    a.Length = 24 + k.data.bytes;
+    a.Data = (unsigned char*)std::malloc(a.Length);
+    std::memcpy(a.Data, "OB2GK1\0\0", 8);
+    u64 g = (u64)galEl, w = k.data.bytes / 8;
+    std::memcpy(a.Data + 8, &g, 8); std::memcpy(a.Data + 16, &w, 8);
+    OB_CUDA(cudaMemcpyAsync(a.Data + 24, k.data.p, k.data.bytes, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    if (!had) s.galois_keys.erase((u64)galEl);                  // the reference does not keep the key it serialises
+    return a;
+}
+void LoadRotationKey(unsigned char* data, unsigned long len, unsigned long galEl) {
+    Scheme& s = S();
+    OB_CHECK(len > 24 && std::memcmp(data, "OB2GK1\0\0", 8) == 0, "LoadRotationKey: not an orion_b200 rotation key blob");
+    u64 w; std::memcpy(&w, data + 16, 8);
+    OB_CHECK(len == 24 + w * 8, "LoadRotationKey: truncated blob");
+    auto k = std::make_unique<EvalKey>();
+    k->data.alloc(w * 8);
+    OB_CUDA(cudaMemcpyAsync(k->data.p, data + 24, w * 8, cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    if (!s.has_galois_key(galEl)) g_lt_keys.insert(galEl);
+    s.galois_keys[galEl] = std::move(k);
+}
+ArrayResultByte SerializeDiagonal(int transform, int diag) {
+    Scheme& s = S();
+    LinearTransform& lt = lt_get(transform);
+    auto it = lt.slot_of.find(diag & ((1 << lt.log_slots) - 1));
+    OB_CHECK(it != lt.slot_of.end(), "SerializeDiagonal: no such diagonal");
+    const size_t bytes = (size_t)lt.W * s.N * 8;
+    ArrayResultByte a;
+    a.Length = 16 + bytes;
+    a.Data = (unsigned char*)std::malloc(a.Length);
+    std::memcpy(a.Data, "OB2DG1\0\0", 8);
+    u64 w = bytes / 8; std::memcpy(a.Data + 8, &w, 8);
+    OB_CUDA(cudaMemcpyAsync(a.Data + 16, lt.diags.u() + (size_t)it->second * lt.W * s.N, bytes, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    return a;
+}
+void LoadPlaintextDiagonal(unsigned char* data, unsigned long len, int transform, unsigned long diag) {
+    Scheme& s = S();
+    LinearTransform& lt = lt_get(transform);
+    auto it = lt.slot_of.find((int)diag & ((1 << lt.log_slots) - 1));
+    OB_CHECK(it != lt.slot_of.end(), "LoadPlaintextDiagonal: no such diagonal");
+    const size_t bytes = (size_t)lt.W * s.N * 8;
+    OB_CHECK(len == 16 + bytes && std::memcmp(data, "OB2DG1\0\0", 8) == 0, "LoadPlaintextDiagonal: bad blob");
+    if (!lt.has_data()) lt.diags.alloc((size_t)lt.diag_idx.size() * bytes);
+    OB_CUDA(cudaMemcpyAsync(lt.diags.u() + (size_t)it->second * lt.W * s.N, data + 16, bytes, cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+}
+void RemovePlaintextDiagonals(int transform) { lt_get(transform).diags.release(); }
+void RemoveRotationKeys(void) {
+    Scheme& s = S();
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    for (u64 g : g_lt_keys) if (!g_eval_keys.count(g)) s.galois_keys.erase(g);
+    g_lt_keys.clear();
+}
+// the drifted Python layer passes what GetLinearTransformRotationKeys returned (PY/lt_evaluator.py:77 <- HG/bindings.py:1879)
+void GenerateConsolidatedRotationKeys(int* galEls, int n) { for (int i = 0; i < n; ++i) GenerateLinearTransformRotationKey(galEls[i]); }
+
+}  // extern "C"

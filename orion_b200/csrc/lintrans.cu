@@ -1,0 +1,218 @@
+// lintrans.cu -- hoisted BSGS diagonal matrix-vector product on the device.
+//
+//   out = sum_j rot_j( sum_i diag'_{j+i} (.) rot_i(ct) ),   diag'_{j+i} = diag_{j+i} rotated right by j
+//
+// Data flow (everything stays in the extended basis QP until the final ModDown, as Lattigo's
+// MultiplyByDiagMatrixBSGS does; reference call site LG/lineartransform.go:96-113):
+//   1. decompose c1 once (hoisting)                                       [beta][W][N]
+//   2. per baby step i != 0: inner product with evk_i, + P*c0, automorphism  -> rot_i  [2][W][N]  (lazy, not / P)
+//      rot_0 = (P*c0, P*c1) with zero P-limbs
+//   3. per giant step j: 128-bit multiply-accumulate of the Montgomery-form diagonals against rot_i,
+//      one REDC per output; j != 0: ModDown the c1 half, key switch it with evk_j (lazy), add the c0 half,
+//      automorphism, accumulate
+//   4. ModDown the accumulator: level and scale bookkeeping only, no rescale (PY/lt_evaluator.py:192 rescales).
+// The reference GPU path instead does one full rotation + plaintext encode per diagonal (HG/bindings.py:1745-1826).
+#include "lintrans.h"
+#include <algorithm>
+#include <cmath>
+
+namespace ob {
+
+namespace {
+constexpr int TPB = 256;
+
+// acc[c][t][x] = REDC( sum_k diag[pairs[k].x][td][x] * rot[pairs[k].y][c][t][x] ),  td = diag limb of t
+__global__ void __launch_bounds__(TPB)
+lt_mac_kernel(const u64* __restrict__ diags, const u64* __restrict__ rots, const int2* __restrict__ pairs, int npairs,
+              u64* __restrict__ acc, int N, int L, int W, int L_lt, int W_lt, int nQ, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
+    const int ci = t < L ? t : nQ + (t - L);
+    const int td = t < L ? t : L_lt + (t - L);
+    const ModConst m = mc[ci];
+    u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
+    for (int k = 0; k < npairs; ++k) {
+        const int2 pr = __ldg(&pairs[k]);
+        const u64 d = diags[((size_t)pr.x * W_lt + td) * N + x];
+        const u64* r = rots + (size_t)pr.y * 2 * W * N;
+        mac128(h0, l0, d, r[(size_t)t * N + x], m.q);
+        mac128(h1, l1, d, r[((size_t)W + t) * N + x], m.q);
+    }
+    acc[(size_t)t * N + x] = mont_redc(h0, l0, m.q, m.qinv_neg);
+    acc[((size_t)W + t) * N + x] = mont_redc(h1, l1, m.q, m.qinv_neg);
+}
+
+// out[p][t][x] = t < L ? (P mod q_t) * c[p][t][x] : 0        (lift of a Q-basis ciphertext to "P * ct" in QP)
+__global__ void __launch_bounds__(TPB)
+lift_times_p_kernel(const u64* __restrict__ c, int c_stride, u64* __restrict__ out, int N, int L, int W,
+                    const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, p = blockIdx.z, x = blockIdx.x * TPB + threadIdx.x;
+    u64 v = 0;
+    if (t < L) { const ulonglong2 w = pmodq[t]; v = shoup_mul(c[((size_t)p * c_stride + t) * N + x], w.x, w.y, mc[t].q); }
+    out[((size_t)p * W + t) * N + x] = v;
+}
+// acc[t][x] += (P mod q_t) * c[t][x]   for t < L
+__global__ void __launch_bounds__(TPB)
+add_times_p_kernel(u64* __restrict__ acc, const u64* __restrict__ c, int N,
+                   const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
+    const u64 q = mc[t].q; const ulonglong2 w = pmodq[t];
+    const size_t o = (size_t)t * N + x;
+    acc[o] = add_mod(acc[o], shoup_mul(c[o], w.x, w.y, q), q);
+}
+
+HandleTable<LinearTransform> g_lts;
+}  // namespace
+
+int lt_push(std::unique_ptr<LinearTransform> lt) { return g_lts.add(std::move(lt)); }
+LinearTransform& lt_get(int id) { return g_lts.get(id, "linear transform"); }
+void lt_delete(int id) { g_lts.del(id); }
+void lt_reset() { if (!g_lts.live.empty()) cudaStreamSynchronize(stream()); g_lts.reset(); }
+
+void bsgs_index(const std::vector<int>& diags, int slots, int N1, std::map<int, std::vector<int>>& index,
+                std::vector<int>& giants, std::vector<int>& babies) {
+    index.clear();
+    std::set<int> g, b;
+    for (int rot : diags) {
+        rot &= (slots - 1);
+        const int j = ((rot / N1) * N1) & (slots - 1), i = rot & (N1 - 1);
+        index[j].push_back(i);
+        g.insert(j); b.insert(i);
+    }
+    for (auto& kv : index) std::sort(kv.second.begin(), kv.second.end());
+    giants.assign(g.begin(), g.end()); babies.assign(b.begin(), b.end());
+}
+
+int find_best_bsgs_ratio(const std::vector<int>& diags, int slots, int log_max_ratio) {
+    const double max_ratio = (double)(1 << log_max_ratio);
+    for (int N1 = 1; N1 < slots; N1 <<= 1) {
+        std::map<int, std::vector<int>> idx; std::vector<int> g, b;
+        bsgs_index(diags, slots, N1, idx, g, b);
+        const double r = (double)((int)g.size() - 1) / (double)((int)b.size() - 1);   // IEEE: x/0 = inf, 0/0 = nan
+        if (r == max_ratio) return N1;
+        if (r < max_ratio) return N1 / 2 > 0 ? N1 / 2 : 1;
+    }
+    return 1;
+}
+
+std::unique_ptr<LinearTransform> lt_build(Scheme& s, const std::map<int, std::vector<double2>>& diagonals, int level,
+                                          scale_t scale, int log_slots, int log_bsgs_ratio) {
+    OB_CHECK(level >= 0 && level <= s.max_level, "linear transform level out of range");
+    OB_CHECK(s.nP > 0, "linear transforms need special primes (LogP)");
+    auto lt = std::make_unique<LinearTransform>();
+    const int slots = 1 << log_slots, N = s.N;
+    lt->level = level; lt->log_slots = log_slots; lt->scale = scale; lt->W = level + 1 + s.nP;
+    for (auto& kv : diagonals) {
+        OB_CHECK((int)kv.second.size() == slots, "diagonal length must equal the slot count");
+        lt->diag_idx.push_back(kv.first & (slots - 1));
+    }
+    std::sort(lt->diag_idx.begin(), lt->diag_idx.end());
+    lt->diag_idx.erase(std::unique(lt->diag_idx.begin(), lt->diag_idx.end()), lt->diag_idx.end());
+    OB_CHECK(lt->diag_idx.size() == diagonals.size(), "duplicate diagonal indices");
+    lt->N1 = log_bsgs_ratio < 0 ? slots : find_best_bsgs_ratio(lt->diag_idx, slots, log_bsgs_ratio);
+    bsgs_index(lt->diag_idx, slots, lt->N1, lt->index, lt->giants, lt->babies);
+    const int nd = (int)lt->diag_idx.size();
+    for (int k = 0; k < nd; ++k) lt->slot_of[lt->diag_idx[k]] = k;
+    std::map<int, int> baby_slot;
+    for (size_t k = 0; k < lt->babies.size(); ++k) baby_slot[lt->babies[k]] = (int)k;
+
+    // encode every diagonal, pre-rotated right by its giant step, at `scale` into QP (Montgomery form)
+    lt->diags.alloc((size_t)nd * lt->W * N * 8);
+    const int chunk = std::max(1, std::min(nd, (int)((256u << 20) / ((size_t)lt->W * N * 8))));
+    std::vector<double2> host((size_t)chunk * slots);
+    DevBuf dv((size_t)chunk * slots * sizeof(double2));
+    std::map<int, const std::vector<double2>*> by_idx;
+    for (auto& kv : diagonals) by_idx[kv.first & (slots - 1)] = &kv.second;
+    for (int k0 = 0; k0 < nd; k0 += chunk) {
+        const int nb = std::min(chunk, nd - k0);
+        for (int k = 0; k < nb; ++k) {
+            const int d = lt->diag_idx[k0 + k], j = ((d / lt->N1) * lt->N1) & (slots - 1);
+            const std::vector<double2>& v = *by_idx[d];
+            double2* dst = host.data() + (size_t)k * slots;
+            for (int x = 0; x < slots; ++x) dst[x] = v[(x - j + slots) & (slots - 1)];
+        }
+        OB_CUDA(cudaMemcpyAsync(dv.p, host.data(), (size_t)nb * slots * sizeof(double2), cudaMemcpyHostToDevice, stream()));
+        OB_CUDA(cudaStreamSynchronize(stream()));
+        s.encode_device_batch(dv.as<double2>(), log_slots, nb, scale, level, true, lt->diags.u() + (size_t)k0 * lt->W * N, true);
+    }
+    for (auto& kv : lt->index) {
+        std::vector<int2> pr;
+        for (int i : kv.second) pr.push_back(make_int2(lt->slot_of[(kv.first + i) & (slots - 1)], baby_slot[i]));
+        DevBuf& b = lt->pairs[kv.first];
+        b.alloc(pr.size() * sizeof(int2));
+        OB_CUDA(cudaMemcpyAsync(b.p, pr.data(), pr.size() * sizeof(int2), cudaMemcpyHostToDevice, stream()));
+        OB_CUDA(cudaStreamSynchronize(stream()));
+    }
+    return lt;
+}
+
+std::vector<u64> lt_galois_elements(Scheme& s, const LinearTransform& lt) {
+    std::set<u64> g;
+    for (int j : lt.giants) if (j) g.insert(s.ctx->galois_element(j));
+    for (int i : lt.babies) if (i) g.insert(s.ctx->galois_element(i));
+    return std::vector<u64>(g.begin(), g.end());
+}
+
+std::unique_ptr<Ciphertext> lt_apply(Scheme& s, const LinearTransform& lt, const Ciphertext& in) {
+    OB_CHECK(lt.has_data(), "linear transform has no encoded diagonals (removed?)");
+    OB_CHECK(in.degree == 1, "EvaluateLinearTransform expects a degree-1 ciphertext");
+    Context& c = *s.ctx;
+    const int level = std::min(in.level, lt.level), L = level + 1, K = c.nP, W = L + K, N = c.N;
+    const int in_stride = in.level + 1;
+    const size_t PW = (size_t)2 * W * N;                       // one QP ciphertext
+    const int nb = (int)lt.babies.size();
+    const ulonglong2* pmodq = c.d_pmodq.as<ulonglong2>();
+
+    // compact c0, c1 at the working level
+    DevBuf ct((size_t)2 * L * N * 8);
+    ew_binary(c, EW_COPY, in.data.u(), in_stride, nullptr, 0, 1, ct.u(), L, 2, L, L);
+    const u64* c0 = ct.u(); const u64* c1 = ct.u() + (size_t)L * N;
+
+    DevBuf digits(s.pev->digits_words(level) * 8), rots((size_t)nb * PW * 8), tmp(PW * 8);
+    bool need_digits = false;
+    for (int i : lt.babies) if (i) need_digits = true;
+    if (need_digits) s.pev->decompose(level, c1, digits.u());
+    for (int k = 0; k < nb; ++k) {
+        const int i = lt.babies[k];
+        u64* r = rots.u() + (size_t)k * PW;
+        if (i == 0) {
+            OB_LAUNCH(lift_times_p_kernel, dim3(N / TPB, W, 2), TPB, 0, stream(), ct.u(), L, r, N, L, W, pmodq, c.dmc());
+            continue;
+        }
+        const u64 g = c.galois_element(i);
+        ks_inner_product(c, level, c1, digits.u(), s.galois_key(g).data.u(), tmp.u(), nullptr, false);
+        OB_LAUNCH(add_times_p_kernel, dim3(N / TPB, L), TPB, 0, stream(), tmp.u(), c0, N, pmodq, c.dmc());
+        automorphism_ntt(c, tmp.u(), r, 2 * W, c.galois_index(g));
+    }
+
+    DevBuf out(PW * 8), acc(PW * 8), u1((size_t)L * N * 8), dig2(s.pev->digits_words(level) * 8), ks(PW * 8), rot(PW * 8);
+    bool first = true;
+    for (auto& kv : lt.index) {
+        const int j = kv.first, np = (int)kv.second.size();
+        u64* dst = (j == 0 && first) ? out.u() : acc.u();
+        OB_LAUNCH(lt_mac_kernel, dim3(N / TPB, W), TPB, 0, stream(), lt.diags.u(), rots.u(), lt.pairs.at(j).as<int2>(), np,
+                  dst, N, L, W, lt.level + 1, lt.W, c.nQ, c.dmc());
+        const u64* contrib = dst;
+        if (j != 0) {
+            const u64 g = c.galois_element(j);
+            s.pev->moddown(level, acc.u() + (size_t)W * N, 1, nullptr, 0, 0, u1.u(), L);
+            s.pev->decompose(level, u1.u(), dig2.u());
+            ks_inner_product(c, level, u1.u(), dig2.u(), s.galois_key(g).data.u(), ks.u(), nullptr, false);
+            // c0 half of the inner sum is added before the automorphism (it is already scaled by P)
+            ew_binary(c, EW_ADD, ks.u(), W, acc.u(), W, 1, ks.u(), W, 1, W, L);
+            automorphism_ntt(c, ks.u(), rot.u(), 2 * W, c.galois_index(g));
+            contrib = rot.u();
+        }
+        if (first) {
+            if (contrib != out.u())
+                OB_CUDA(cudaMemcpyAsync(out.p, contrib, PW * 8, cudaMemcpyDeviceToDevice, stream()));
+            first = false;
+        } else {
+            ew_binary(c, EW_ADD, out.u(), W, contrib, W, 2, out.u(), W, 2, W, L);
+        }
+    }
+    auto res = s.new_ct(level, 1, in.scale * lt.scale, in.log_slots);
+    s.pev->moddown(level, out.u(), 2, nullptr, 0, 0, res->data.u(), L);
+    return res;
+}
+
+}  // namespace ob
