@@ -118,7 +118,9 @@ int GenerateMonomial(float* coeffs, int n);
 int GenerateChebyshev(float* coeffs, int n);
 int EvaluatePolynomial(int ct, int poly, unsigned long outScale);
 int GetPolyDepth(int poly);                                           /* python/poly_evaluator.py:59 */
-ArrayResultDouble GenerateMinimaxSignCoeffs(int* degrees, int n, int prec, int logalpha, int logerr, int debug);
+int B200_GeneratePolynomialF64(const double* coeffs, int n, int chebyshev);   /* float64 coefficients */
+/* GenerateMinimaxSignCoeffs (LG/polyeval.go:91-167) is host-only multi-precision Remez: it is provided by the Python
+ * binding layer (orion_b200/minimax.py, B200Library.GenerateMinimaxSignCoeffs), not by this shared library. */
 
 /* ---- bootstrapping: LG/bootstrapper.go:19-93 ---- */
 void NewBootstrapper(int* logPs, int n, int numSlots);

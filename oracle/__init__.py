@@ -98,6 +98,12 @@ def lib():
         "orc_sample_ternary_hw": ([c_int, c_int, c_u64, c_u64, i64p], None),
         "orc_small_to_rns": ([c_vp, c_int, i64p, u64p], None),
         "orc_gaussian_cdt": ([u64p, c_int], c_int),
+        "orc_roots": ([c_int, f64p, f64p], None),
+        "orc_special_ifft": ([f64p, f64p, c_int, c_int], None),
+        "orc_special_fft": ([f64p, f64p, c_int, c_int], None),
+        "orc_encode_round": ([c_vp, f64p, f64p, c_int, ctypes.c_double, intp, c_int, u64p], None),
+        "orc_scaled_const_rns": ([c_vp, ctypes.c_double, ctypes.c_longdouble, intp, c_int, u64p], None),
+        "orc_decode_crt": ([c_vp, u64p, c_int, ctypes.c_double, c_int, f64p, f64p], None),
     }
     for name, (args, res) in sig.items():
         f = getattr(L, name)

@@ -104,6 +104,15 @@ void orc_sample_ternary_hw(int N, int h, u64 seed, u64 stream, int64_t *out); /*
 void orc_small_to_rns(const orc_ctx *c, int mod_idx, const int64_t *in, u64 *out);
 int  orc_gaussian_cdt(u64 *table, int max_entries);                     /* the CDT both sides use */
 
+/* ---- scheme-level pieces (ckks_oracle_ckks.c): canonical-embedding FFT, encode rounding, decode CRT ---- */
+void orc_roots(int M, double *re, double *im);
+void orc_special_ifft(double *re, double *im, int log_slots, int M);
+void orc_special_fft(double *re, double *im, int log_slots, int M);
+void orc_encode_round(const orc_ctx *c, const double *re, const double *im, int log_slots, double scale,
+                      const int *mods, int nmods, u64 *out);
+void orc_scaled_const_rns(const orc_ctx *c, double v, long double cscale, const int *mods, int n, u64 *out);
+void orc_decode_crt(const orc_ctx *c, const u64 *coeffs, int level, double scale, int log_slots, double *re, double *im);
+
 #ifdef __cplusplus
 }
 #endif

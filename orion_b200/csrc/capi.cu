@@ -5,6 +5,8 @@
 // Declarations with per-function reference citations: include/orion_b200_scheme.h.
 #include "scheme.h"
 #include "lintrans.h"
+#include "polyeval.h"
+#include "bootstrap.h"
 #include "../../include/orion_b200_scheme.h"
 #include <cmath>
 #include <random>
@@ -51,12 +53,12 @@ void NewScheme(int logN, int* logQ, int lenQ, int* logP, int lenP, int logScale,
     p.conjugate_invariant = (rt != "standard");
     u64 seed = g_seed;
     if (!g_seed_set) { std::random_device rd; seed = ((u64)rd() << 32) ^ rd(); }   // OS randomness, as Lattigo does
-    lt_reset();
+    lt_reset(); poly_reset(); boot_reset();
     g_scheme.reset();
     g_scheme = std::make_unique<Scheme>(p, seed);
 }
 void DeleteScheme(void) {
-    lt_reset();
+    lt_reset(); poly_reset(); boot_reset();
     g_scheme.reset();
 }
 void FreeCArray(void* p) { std::free(p); }
@@ -323,4 +325,33 @@ void RemoveRotationKeys(void) {
 // the drifted Python layer passes what GetLinearTransformRotationKeys returned (PY/lt_evaluator.py:77 <- HG/bindings.py:1879)
 void GenerateConsolidatedRotationKeys(int* galEls, int n) { for (int i = 0; i < n; ++i) GenerateLinearTransformRotationKey(galEls[i]); }
 
+}  // extern "C"
+
+// ---------------------------------------------------------------- polynomial evaluation (LG/polyeval.go:33-84)
+extern "C" {
+void NewPolynomialEvaluator(void) { S(); }
+static int make_poly(float* coeffs, int n, bool cheb) {
+    OB_CHECK(n >= 1, "polynomial needs at least one coefficient");
+    auto p = std::make_unique<Polynomial>();
+    p->chebyshev = cheb;
+    p->coeffs.assign(coeffs, coeffs + n);
+    return poly_push(std::move(p));
+}
+int GenerateMonomial(float* coeffs, int n) { return make_poly(coeffs, n, false); }
+int GenerateChebyshev(float* coeffs, int n) { return make_poly(coeffs, n, true); }
+int B200_GeneratePolynomialF64(const double* coeffs, int n, int chebyshev) {
+    auto p = std::make_unique<Polynomial>();
+    p->chebyshev = chebyshev != 0;
+    p->coeffs.assign(coeffs, coeffs + n);
+    return poly_push(std::move(p));
+}
+int EvaluatePolynomial(int ct, int poly, unsigned long outScale) {
+    return push_ct(poly_evaluate(S(), CT(ct), poly_get(poly), (scale_t)outScale));
+}
+int GetPolyDepth(int poly) { return poly_depth(poly_get(poly)); }
+
+// ---------------------------------------------------------------- bootstrapping (LG/bootstrapper.go:19-93)
+void NewBootstrapper(int* logPs, int n, int numSlots) { boot_new(S(), std::vector<int>(logPs, logPs + n), numSlots); }
+int Bootstrap(int ct, int numSlots) { return push_ct(boot_apply(S(), CT(ct), numSlots)); }
+void DeleteBootstrappers(void) { boot_reset(); }
 }  // extern "C"

@@ -1,0 +1,237 @@
+"""GPU parity of the scheme layer (keys, encode, encrypt, evaluator ops, linear transforms) against the CPU oracle,
+through the Orion-facing C ABI.  Same seed + same order of sampling events => bit-identical keys and ciphertexts."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+PARAMS = dict(logN=12, logQ=[45, 30, 30, 30, 30], logP=[45, 45], log_scale=30, h=64)
+SEED = 20261104
+
+
+@pytest.fixture(scope="module")
+def pair(orc, b200lib):
+    from oracle.scheme import OScheme
+    from orion_b200.bindings import B200Library
+    p = PARAMS
+    B = B200Library()
+    B.B200_SetSeed(SEED)
+    B.NewScheme(p["logN"], p["logQ"], p["logP"], p["log_scale"], p["h"], "standard", "", "none")
+    O = OScheme(p["logN"], p["logQ"], p["logP"], p["log_scale"], p["h"], SEED)
+    B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey(); B.GenerateEvaluationKeys()
+    O.gen_secret_key(); O.gen_public_key(); O.gen_relin_key()
+    B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor()
+    yield B, O
+    B.DeleteScheme()
+
+
+def export_ct(B, O, ct):
+    level, deg = B.GetCiphertextLevel(ct), B.GetCiphertextDegree(ct)
+    out = np.empty((deg + 1, level + 1, O.N), dtype=np.uint64)
+    B.B200_ExportCiphertext(ct, out)
+    return out
+
+
+def export_pt(B, O, pt):
+    level = B.GetPlaintextLevel(pt)
+    out = np.empty((level + 1, O.N), dtype=np.uint64)
+    B.B200_ExportPlaintext(pt, out)
+    return out
+
+
+def test_keys_bit_exact(pair):
+    B, O = pair
+    sk = np.empty(O.N, dtype=np.int64)
+    B.B200_ExportSecretKey(sk)
+    assert np.array_equal(sk, O.sk_coeffs)
+    assert int(np.count_nonzero(sk)) == PARAMS["h"]
+    pk = np.empty((2, O.nmod, O.N), dtype=np.uint64)
+    B.B200_ExportPublicKey(pk)
+    assert np.array_equal(pk, O.pk)
+    beta = O.ctx.num_digits(O.max_level)
+    rlk = np.empty((beta, 2, O.nmod, O.N), dtype=np.uint64)
+    B.B200_ExportRelinKey(rlk)
+    assert np.array_equal(rlk, O.rlk)
+    assert B.GetModuliChain() == O.Q
+
+
+def test_encode_decode(pair):
+    B, O = pair
+    rng = np.random.default_rng(1)
+    slots = O.N // 2
+    v = rng.uniform(-1, 1, slots).astype(np.float32)
+    for level in (O.max_level, 1, 0):
+        scale = 1 << 30
+        pt = B.Encode(v.tolist(), level, scale)
+        assert B.GetPlaintextLevel(pt) == level and B.GetPlaintextScale(pt) == scale and B.GetPlaintextSlots(pt) == slots
+        opt = O.encode(v.astype(np.float64), level, scale)
+        assert np.array_equal(export_pt(B, O, pt), opt.data), "encode level %d" % level
+        dec = np.array(B.Decode(pt))
+        assert np.max(np.abs(dec - v)) < 1e-6
+        odec = O.decode(opt)
+        re, im = np.empty(slots), np.empty(slots)
+        B.B200_DecodeF64(pt, re, im)
+        assert np.array_equal(re, odec.real) and np.array_equal(im, odec.imag)
+        B.DeletePlaintext(pt)
+    # ragged input: fewer values than slots are zero-padded
+    pt = B.Encode(v[:100].tolist(), 2, 1 << 30)
+    assert np.array_equal(export_pt(B, O, pt), O.encode(v[:100].astype(np.float64), 2, 1 << 30).data)
+    B.DeletePlaintext(pt)
+
+
+def test_encrypt_ops(pair):
+    B, O = pair
+    rng = np.random.default_rng(2)
+    slots = O.N // 2
+    x = rng.uniform(-1, 1, slots).astype(np.float32)
+    y = rng.uniform(-1, 1, slots).astype(np.float32)
+    scale = 1 << 30
+    L = O.max_level
+    ptx, pty = B.Encode(x.tolist(), L, scale), B.Encode(y.tolist(), L, scale)
+    optx, opty = O.encode(x.astype(np.float64), L, scale), O.encode(y.astype(np.float64), L, scale)
+    ctx_, cty = B.Encrypt(ptx), B.Encrypt(pty)
+    octx, octy = O.encrypt(optx), O.encrypt(opty)
+    assert np.array_equal(export_ct(B, O, ctx_), octx.data)
+    assert np.array_equal(export_ct(B, O, cty), octy.data)
+
+    def dec(ct):
+        p = B.Decrypt(ct); out = np.array(B.Decode(p)); B.DeletePlaintext(p); return out
+
+    assert np.max(np.abs(dec(ctx_) - x)) < 1e-4
+    # add / sub / plaintext ops
+    s = B.AddCiphertextNew(ctx_, cty)
+    assert np.array_equal(export_ct(B, O, s), O.add(octx, octy).data)
+    d = B.SubCiphertextNew(ctx_, cty)
+    assert np.array_equal(export_ct(B, O, d), O.add(octx, octy, sub=True).data)
+    ap = B.AddPlaintextNew(ctx_, pty)
+    assert np.array_equal(export_ct(B, O, ap), O.add(octx, opty).data)
+    sp = B.SubPlaintextNew(ctx_, pty)
+    assert np.array_equal(export_ct(B, O, sp), O.add(octx, opty, sub=True).data)
+    # scalar ops
+    a1 = B.AddScalarNew(ctx_, 0.375)
+    assert np.array_equal(export_ct(B, O, a1), O.add_const(octx, 0.375).data)
+    a2 = B.SubScalarNew(ctx_, 1.5)
+    assert np.array_equal(export_ct(B, O, a2), O.add_const(octx, -1.5).data)
+    m1 = B.MulScalarIntNew(ctx_, -3)
+    assert np.array_equal(export_ct(B, O, m1), O.mul_int(octx, -3).data)
+    ng = B.Negate(ctx_)
+    assert np.array_equal(export_ct(B, O, ng), O.mul_int(octx, -1).data)
+    m2 = B.MulScalarFloatNew(ctx_, 0.3)
+    om2 = O.mul_float(octx, float(np.float32(0.3)))
+    assert np.array_equal(export_ct(B, O, m2), om2.data)
+    m2 = B.Rescale(m2)
+    om2 = O.rescale(om2)
+    assert np.array_equal(export_ct(B, O, m2), om2.data)
+    assert B.GetCiphertextLevel(m2) == L - 1
+    assert np.max(np.abs(dec(m2) - np.float32(0.3) * x)) < 1e-4
+    # ct x pt, ct x ct (+ relinearisation) and rescale
+    mp = B.MulPlaintextNew(ctx_, pty)
+    omp = O.mul_pt(octx, opty)
+    assert np.array_equal(export_ct(B, O, mp), omp.data)
+    mp = B.Rescale(mp); omp = O.rescale(omp)
+    assert np.array_equal(export_ct(B, O, mp), omp.data)
+    assert np.max(np.abs(dec(mp) - x * y)) < 1e-4
+    mc = B.MulRelinCiphertextNew(ctx_, cty)
+    omc = O.mul_relin(octx, octy)
+    assert np.array_equal(export_ct(B, O, mc), omc.data)
+    mc = B.Rescale(mc); omc = O.rescale(omc)
+    assert np.array_equal(export_ct(B, O, mc), omc.data)
+    assert np.max(np.abs(dec(mc) - x * y)) < 1e-4
+    # level mismatch: operands are aligned by dropping limbs
+    mix = B.AddCiphertextNew(mc, ctx_)
+    assert B.GetCiphertextLevel(mix) == L - 1
+    # rotations (keys generated on demand, in the same order on both sides)
+    for rot in (1, 7, -2):
+        r = B.RotateNew(ctx_, rot)
+        orr = O.rotate(octx, rot)
+        assert np.array_equal(export_ct(B, O, r), orr.data), "rotate %d" % rot
+        assert np.max(np.abs(dec(r) - np.roll(x, -rot))) < 1e-4
+        B.DeleteCiphertext(r)
+    cj = B.B200_Conjugate(ctx_)
+    assert np.array_equal(export_ct(B, O, cj), O.conjugate(octx).data)
+    # handle table: smallest free integer is reused
+    live = B.GetLiveCiphertexts()
+    B.DeleteCiphertext(s)
+    t = B.CloneCiphertext(ctx_)
+    assert t == s and sorted(B.GetLiveCiphertexts()) == sorted(live)
+
+
+def test_linear_transform(pair):
+    B, O = pair
+    rng = np.random.default_rng(3)
+    slots = O.N // 2
+    level = 3
+    scale = 1 << 30
+    x = rng.uniform(-1, 1, slots).astype(np.float32)
+    diag_idx = list(range(0, 24)) + [slots - 3, slots - 1, 100, 1000]
+    diags = {d: rng.uniform(-1, 1, slots).astype(np.float32) for d in diag_idx}
+    flat = np.concatenate([diags[d] for d in diag_idx])
+    pt = B.Encode(x.tolist(), level, scale)
+    ct = B.Encrypt(pt)
+    oct_ = O.encrypt(O.encode(x.astype(np.float64), level, scale))
+    assert np.array_equal(export_ct(B, O, ct), oct_.data)
+    B.NewLinearTransformEvaluator()
+    lt = B.GenerateLinearTransform(diag_idx, flat, level, 2.0, "none")
+    olt = O.lt_build({d: v.astype(np.float64) for d, v in diags.items()}, level, O.Q[level], log_bsgs_ratio=0)
+    gal = B.GetLinearTransformRotationKeys(lt)
+    assert sorted(gal) == O.lt_galois_elements(olt)
+    for g in sorted(gal):
+        B.GenerateLinearTransformRotationKey(g)
+        O.galois_key(g)
+    out = B.EvaluateLinearTransform(lt, ct)
+    oout = O.lt_apply(olt, oct_)
+    assert np.array_equal(export_ct(B, O, out), oout.data)
+    out = B.Rescale(out)
+    p = B.Decrypt(out)
+    got = np.array(B.Decode(p))
+    want = np.zeros(slots)
+    for d, v in diags.items():
+        want += v.astype(np.float64) * np.roll(x.astype(np.float64), -d)
+    assert np.max(np.abs(got - want)) < 1e-3
+    B.DeleteLinearTransform(lt)
+
+
+def test_polynomial_evaluation(orc, b200lib):
+    """Depth-optimal PS evaluation: output level = in - ceil(log2(d+1)), scale == requested, values match numpy."""
+    from orion_b200.bindings import B200Library
+    B = B200Library()
+    B.B200_SetSeed(7)
+    logq = [50] + [40] * 7
+    B.NewScheme(13, logq, [51, 51], 40, 192, "standard", "", "none")
+    B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey()
+    B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor(); B.NewPolynomialEvaluator()
+    Q = B.GetModuliChain()
+    rng = np.random.default_rng(5)
+    slots = 4096
+    x = rng.uniform(-1, 1, slots)
+    L = len(logq) - 1
+    pt = B.B200_EncodeF64(x, slots, L, float(1 << 40))
+    ct = B.Encrypt(pt)
+
+    def dec(c):
+        p = B.Decrypt(c)
+        re, im = np.empty(slots), np.empty(slots)
+        B.B200_DecodeF64(p, re, im)
+        B.DeletePlaintext(p)
+        return re
+
+    for deg, cheb in ((1, False), (3, False), (7, False), (12, False), (15, True), (31, True), (63, True), (27, True)):
+        coeffs = rng.uniform(-1, 1, deg + 1) / (1.0 if cheb else np.arange(1, deg + 2))
+        poly = B.B200_GeneratePolynomialF64(np.ascontiguousarray(coeffs), deg + 1, 1 if cheb else 0)
+        depth = int(np.ceil(np.log2(deg + 1)))
+        assert B.GetPolyDepth(poly) == depth
+        out_level = L - depth
+        out_scale = Q[out_level]                      # what orion's ReLU asks for (activation.py:253-255)
+        out = B.EvaluatePolynomial(ct, poly, out_scale)
+        assert B.GetCiphertextLevel(out) == out_level
+        assert B.GetCiphertextScale(out) == out_scale
+        want = np.polynomial.chebyshev.chebval(x, coeffs) if cheb else np.polynomial.polynomial.polyval(x, coeffs)
+        err = np.max(np.abs(dec(out) - want))
+        assert err < 1e-5, "degree %d cheb=%s err=%g" % (deg, cheb, err)
+        B.DeleteCiphertext(out)
+    # float32 entry points used by orion (coefficients ascending)
+    c32 = [0.5, 0.25, 0.0, -0.125]
+    pm = B.GenerateMonomial(c32)
+    out = B.EvaluatePolynomial(ct, pm, 1 << 40)
+    assert np.max(np.abs(dec(out) - np.polynomial.polynomial.polyval(x, c32))) < 1e-5
+    B.DeleteScheme()
