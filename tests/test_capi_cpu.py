@@ -1,0 +1,75 @@
+"""CPU tests of the drop-in boundary: the shared library loads without a GPU and exports every symbol the headers
+declare; host-only entry points agree with the oracle; the product never imports the oracle."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    names = []
+    for h in ("orion_b200.h", "orion_b200_scheme.h"):
+        src = open(os.path.join(ROOT, "include", h)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        for m in re.finditer(r"^[A-Za-z_][\w \*]*?[\s\*]+(\w+)\s*\([^;{]*\)\s*;", src, flags=re.M):
+            names.append(m.group(1))
+    return sorted(set(names))
+
+
+def test_library_exports_every_declared_symbol(b200lib):
+    lib = ctypes.CDLL(b200lib.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) > 110
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    # and the two Python signature tables cover exactly the declared surface
+    from orion_b200.bindings import SCHEME_SIGNATURES
+    bound = set(SCHEME_SIGNATURES) | set(b200lib.RAW_SIGNATURES)
+    assert set(names) <= bound, sorted(set(names) - bound)
+
+
+def test_host_only_entry_points_match_oracle(b200lib, orc):
+    for logN, lq, lp in ((13, [29, 26, 26, 26, 26, 26], [29, 29]), (14, [60, 30, 30, 30], [60, 60]),
+                         (16, [60] + [45] * 23, [61, 61, 61])):
+        assert b200lib.gen_moduli(lq, lp, logN + 1) == orc.gen_moduli(lq, lp, logN + 1)
+    lib = b200lib.load()
+    Q, _ = orc.gen_moduli([45, 30], [], 14)
+    for q in Q:
+        assert lib.B200_FindPsi(q, 1 << 14) == orc.lib().orc_psi(q, 1 << 14)
+    assert lib.B200_DeviceCount() >= 0
+
+
+def test_compute_without_gpu_fails_loudly(b200lib):
+    if b200lib.load().B200_DeviceCount() > 0:
+        return
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from orion_b200 import raw\n"
+            "raw.RawContext(12, [1099511480321], [])\n" % ROOT)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
+    assert r.returncode != 0
+    assert "no CUDA device" in r.stderr and "no CPU path" in r.stderr
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "orion_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h", ".cuh")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f
+                assert "ckks_oracle" not in src.replace("oracle/ckks_oracle.c orc_rng_u64", ""), f
+    r = subprocess.run(["ldd", os.path.join(pkg, "liborion_b200.so")], capture_output=True, text=True)
+    assert "oracle" not in r.stdout
+
+
+def test_binding_marshalling_shapes():
+    from orion_b200.bindings import SCHEME_SIGNATURES, _flat_argtypes
+    # NewScheme(logN, logQ*, lenQ, logP*, lenP, logScale, h, ringType, keysPath, ioMode): lattigo/scheme.go:35-44
+    assert len(_flat_argtypes(SCHEME_SIGNATURES["NewScheme"][0])) == 10
+    assert len(_flat_argtypes(SCHEME_SIGNATURES["GenerateLinearTransform"][0])) == 7
+    assert len(_flat_argtypes(SCHEME_SIGNATURES["Encode"][0])) == 4

@@ -1,0 +1,191 @@
+"""CPU tests: pin the oracle against the reference's golden vectors and check it against exact big-integer math."""
+import os
+
+import numpy as np
+import pytest
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ntt_kat.npz")
+
+
+def test_ntt_against_reference_golden_vectors(orc):
+    """tests/golden/ntt_kat.npz was produced by the reference's own CPU NTT (GPU-NTT ntt_cpu.cu) on its KAT pools."""
+    g = np.load(GOLD)
+    L = orc.lib()
+    for logn in (10, 11, 12, 13):
+        q, psi = [int(x) for x in g["logn%d_prime_psi" % logn]]
+        c = orc.Ctx(logn, [q], 1, 0, psi=[psi])
+        a = g["logn%d_in" % logn].copy()
+        f = a.copy(); L.orc_ntt(c.h, 0, orc.P(f))
+        assert np.array_equal(f, g["logn%d_fwd" % logn])
+        i = a.copy(); L.orc_intt(c.h, 0, orc.P(i))
+        assert np.array_equal(i, g["logn%d_inv" % logn])
+    # NTT . pointwise . INTT == the reference's schoolbook product (method of test_cpu_merge_ntt.cu:69-101)
+    q, psi = [int(x) for x in g["logn10_prime_psi"]]
+    c = orc.Ctx(10, [q], 1, 0, psi=[psi])
+    a, b = g["school_a"].copy(), g["school_b"].copy()
+    L.orc_ntt(c.h, 0, orc.P(a)); L.orc_ntt(c.h, 0, orc.P(b))
+    out = np.empty_like(a); L.orc_mul(c.h, 0, orc.P(a), orc.P(b), orc.P(out))
+    L.orc_intt(c.h, 0, orc.P(out))
+    assert np.array_equal(out, g["school_c"])
+
+
+def test_ntt_against_live_reference_when_present(orc):
+    R = orc.ref()
+    if R is None:
+        pytest.skip("oracle/_ref not built on this machine")
+    import ctypes
+    L = orc.lib()
+    rng = np.random.default_rng(5)
+    for logn in (10, 14):
+        p, w, psi = ctypes.c_ulonglong(), ctypes.c_ulonglong(), ctypes.c_ulonglong()
+        R.ref_ntt_pool(logn, p, w, psi)
+        c = orc.Ctx(logn, [p.value], 1, 0, psi=[psi.value])
+        a = rng.integers(0, p.value, size=1 << logn, dtype=np.uint64)
+        ref = np.zeros_like(a); R.ref_ntt_forward(logn, p.value, psi.value, orc.P(a), orc.P(ref))
+        b = a.copy(); L.orc_ntt(c.h, 0, orc.P(b))
+        assert np.array_equal(b, ref)
+
+
+def test_prime_chain_properties(orc):
+    L = orc.lib()
+    for logN, lq, lp in ((13, [29, 26, 26, 26, 26, 26], [29, 29]), (16, [60] + [45] * 5, [61, 61, 61])):
+        Q, P = orc.gen_moduli(lq, lp, logN + 1)
+        allp = Q + P
+        assert len(set(allp)) == len(allp)
+        for p, bits in zip(allp, lq + lp):
+            assert L.orc_is_prime(p) and p % (2 << logN) == 1
+            assert abs(p.bit_length() - bits) <= 1
+            psi = L.orc_psi(p, 2 << logN)
+            assert pow(psi, 1 << logN, p) == p - 1            # primitive 2N-th root
+    # alternating order: nearest to 2^bits first
+    out = np.zeros(4, dtype=np.uint64)
+    L.orc_gen_ntt_primes(30, 1 << 14, 4, None, 0, orc.P(out))
+    d = [abs(int(x) - (1 << 30)) for x in out]
+    assert d == sorted(d)
+
+
+def test_modular_fast_paths_match_bigint(orc):
+    L = orc.lib()
+    rng = np.random.default_rng(0)
+    for bits in (26, 30, 45, 60, 61):
+        Q, _ = orc.gen_moduli([bits], [], 14)
+        q = Q[0]
+        c = orc.Ctx(13, [q], 1, 0)
+        a = rng.integers(0, q, size=8192, dtype=np.uint64)
+        b = rng.integers(0, q, size=8192, dtype=np.uint64)
+        a[:3] = [0, q - 1, q - 1]; b[:3] = [q - 1, q - 1, 1]
+        out = np.empty_like(a)
+        L.orc_mul(c.h, 0, orc.P(a), orc.P(b), orc.P(out))
+        want = np.array([(int(x) * int(y)) % q for x, y in zip(a[:512], b[:512])], dtype=np.uint64)
+        assert np.array_equal(out[:512], want)
+        L.orc_mul_scalar(c.h, 0, orc.P(a), q - 2, orc.P(out))
+        want = np.array([(int(x) * (q - 2)) % q for x in a[:512]], dtype=np.uint64)
+        assert np.array_equal(out[:512], want)
+
+
+def test_base_conversion_is_exact_crt(orc):
+    """out_t == (x - v*Q) mod p_t with x the CRT lift in [0,Q) and v in {0,1} (the float64 overflow estimate)."""
+    rng = np.random.default_rng(1)
+    Q, P = orc.gen_moduli([45, 40, 40], [50, 50], 13)
+    c = orc.Ctx(12, Q + P, 3, 2)
+    src, dst = [0, 1, 2], [3, 4]
+    a = c.uniform_poly(rng, src)
+    out = c.baseconv(a, src, dst)
+    big = Q[0] * Q[1] * Q[2]
+    for x in range(0, 4096, 97):
+        val = 0
+        for i in range(3):
+            qi = Q[i]; m = big // qi
+            val += int(a[i][x]) * pow(m, -1, qi) % qi * m
+        val %= big
+        for t, p in enumerate(P):
+            assert int(out[t][x]) in (val % p, (val - big) % p)
+    # centred variant rounds to the representative in (-Q/2, Q/2]
+    outc = c.baseconv(a, src, dst, centered=True)
+    for x in range(0, 4096, 97):
+        val = 0
+        for i in range(3):
+            qi = Q[i]; m = big // qi
+            val += int(a[i][x]) * pow(m, -1, qi) % qi * m
+        val %= big
+        cen = val - big if val > big // 2 else val
+        for t, p in enumerate(P):
+            assert int(outc[t][x]) in (cen % p, (cen + big) % p, (cen - big) % p)
+
+
+def test_rescale_is_rounded_division(orc):
+    rng = np.random.default_rng(2)
+    Q, _ = orc.gen_moduli([45, 30, 30], [], 13)
+    c = orc.Ctx(12, Q, 3, 0)
+    coef = c.uniform_poly(rng, [0, 1, 2])
+    # build a consistent RNS value: pick x in [0, Q), reduce
+    big = Q[0] * Q[1] * Q[2]
+    xs = [int(rng.integers(0, 1 << 62)) * int(rng.integers(0, 1 << 40)) % big for _ in range(4096)]
+    for i in range(3):
+        coef[i] = np.array([x % Q[i] for x in xs], dtype=np.uint64)
+    ntt = c.ntt(coef, [0, 1, 2])
+    out = c.ntt(c.rescale(2, ntt), [0, 1], inverse=True)
+    for k in range(0, 4096, 61):
+        x = xs[k]
+        cen = x - big if x > big // 2 else x
+        want = (2 * cen + Q[2]) // (2 * Q[2])                   # round(cen / q_last), ties up
+        for i in range(2):
+            assert int(out[i][k]) in (want % Q[i], (want - 1) % Q[i], (want + 1) % Q[i])
+            assert (int(out[i][k]) - want) % Q[i] in (0, 1, Q[i] - 1)
+
+
+def test_keyswitch_decrypts_correctly(orc):
+    """End-to-end property of the hybrid key switch with real keys: Dec_s(KS_{s'->s}(c1)) ~ c1 * s'."""
+    from oracle.scheme import OScheme
+    S = OScheme(12, [45, 30, 30, 30], [45, 45], 30, 64, 99)
+    S.gen_secret_key(); S.gen_public_key(); S.gen_relin_key()
+    rng = np.random.default_rng(3)
+    slots = S.N // 2
+    x = rng.uniform(-1, 1, slots)
+    ct = S.encrypt(S.encode(x, 3, 1 << 30))
+    dec = S.decode(S.decrypt(ct))
+    assert np.max(np.abs(dec.real - x)) < 1e-5
+    r = S.rotate(ct, 5)
+    assert np.max(np.abs(S.decode(S.decrypt(r)).real - np.roll(x, -5))) < 1e-4
+    m = S.rescale(S.mul_relin(ct, ct))
+    assert np.max(np.abs(S.decode(S.decrypt(m)).real - x * x)) < 1e-4
+    cj = S.conjugate(ct)
+    assert np.max(np.abs(S.decode(S.decrypt(cj)).real - x)) < 1e-4
+
+
+def test_linear_transform_oracle_matches_cleartext(orc):
+    from oracle.scheme import OScheme
+    S = OScheme(12, [45, 30, 30], [45, 45], 30, 64, 5)
+    S.gen_secret_key(); S.gen_public_key()
+    rng = np.random.default_rng(4)
+    slots = S.N // 2
+    x = rng.uniform(-1, 1, slots)
+    diags = {d: rng.uniform(-1, 1, slots) for d in [0, 1, 2, 3, 5, 8, 9, slots - 1]}
+    lt = S.lt_build(diags, 2, S.Q[2])
+    for g in S.lt_galois_elements(lt):
+        S.galois_key(g)
+    out = S.rescale(S.lt_apply(lt, S.encrypt(S.encode(x, 2, 1 << 30))))
+    want = sum(v * np.roll(x, -d) for d, v in diags.items())
+    assert np.max(np.abs(S.decode(S.decrypt(out)).real - want)) < 1e-3
+
+
+def test_encode_decode_roundtrip_and_sampling(orc):
+    from oracle.scheme import OScheme
+    S = OScheme(12, [50, 40], [], 40, 32, 1)
+    rng = np.random.default_rng(6)
+    v = rng.uniform(-3, 3, S.N // 2) + 1j * rng.uniform(-3, 3, S.N // 2)
+    for level in (0, 1):
+        d = S.decode(S.encode(v, level, 1 << 40))
+        assert np.max(np.abs(d - v)) < 1e-8
+    # sparse slots
+    d = S.decode(S.encode(v[:256], 1, 1 << 40, log_slots=8))
+    assert np.max(np.abs(d - v[:256])) < 1e-8
+    # samplers: determinism, Hamming weight, Gaussian moments
+    L = orc.lib()
+    a = S._ternary(7); b = S._ternary(7)
+    assert np.array_equal(a, b) and np.count_nonzero(a) == 32 and set(np.unique(a)) <= {-1, 0, 1}
+    g = np.empty(1 << 16, dtype=np.int64)
+    L.orc_sample_gaussian_i64(1 << 16, 1, 2, orc.P(g, orc.i64p))
+    assert abs(g.mean()) < 0.05 and abs(g.std() - 3.2) < 0.05 and np.abs(g).max() <= 19
+    u = S._uniform([0], 3)[0]
+    assert u.max() < S.Q[0] and abs(float(u.mean()) / S.Q[0] - 0.5) < 0.02
