@@ -59,6 +59,8 @@ struct Context {
     u64 galois_element(int rot) const;                // 5^rot mod 2N
     u64 galois_conj() const { return 2ull * N - 1; }
 
+    std::vector<std::unique_ptr<DevBuf>> misc;        // small device tables owned by the context (launch descriptors)
+
   private:
     std::map<std::vector<uint32_t>, std::unique_ptr<DevBuf>> limb_cache_;
     std::map<std::vector<int>, std::unique_ptr<BaseConv>> bc_cache_;

@@ -39,6 +39,7 @@ const KsPlan& PolyEvaluator::ks_plan(int level) {
         p->digit_src_off.push_back(s0);
     }
     p->ntt_digits = make_ntt_plan(c, dl);
+    p->modup_all = make_baseconv_batch(c, p->modup, p->digit_src_off, std::vector<int>(beta, 0));
     std::vector<int> psrc, qdst, qoff;
     for (int k = 0; k < K; ++k) psrc.push_back(c.nQ + k);
     for (int i = 0; i < L; ++i) { qdst.push_back(i); qoff.push_back(i); }
@@ -52,6 +53,12 @@ const KsPlan& PolyEvaluator::ks_plan(int level) {
                 nc.push_back(LimbDesc{(uint32_t)(pp * L + i), (uint32_t)(pp * L + i), (uint32_t)i, 0});
         }
         p->intt_p[polys] = make_ntt_plan(c, ip);
+        {
+            std::vector<BaseConvPlan> pl(polys, p->moddown);
+            std::vector<int> io, ob;
+            for (int pp = 0; pp < polys; ++pp) { io.push_back(pp * K); ob.push_back(pp * L); }
+            p->moddown_b[polys] = make_baseconv_batch(c, pl, io, ob);
+        }
         p->ntt_conv[polys] = make_ntt_plan(c, nc);
     }
     return *plans_.emplace(level, std::move(p)).first->second;
@@ -61,8 +68,7 @@ void PolyEvaluator::decompose(int level, const u64* c1_ntt, u64* digits) {
     const KsPlan& p = ks_plan(level);
     DevBuf coef((size_t)p.L * ctx.N * 8);
     ntt_inverse(ctx, c1_ntt, coef.u(), p.intt_c1);
-    for (int j = 0; j < p.beta; ++j)
-        base_convert(ctx, p.modup[j], coef.u() + (size_t)p.digit_src_off[j] * ctx.N, digits, false);
+    base_convert_batch(ctx, p.modup_all, coef.u(), digits, false);
     ntt_forward(ctx, digits, digits, p.ntt_digits);
 }
 
@@ -73,8 +79,7 @@ void PolyEvaluator::moddown(int level, const u64* acc, int polys, const u64* add
     const size_t N = ctx.N;
     DevBuf pc((size_t)polys * p.K * N * 8), conv((size_t)polys * p.L * N * 8);
     ntt_inverse(ctx, acc, pc.u(), p.intt_p[polys]);
-    for (int pp = 0; pp < polys; ++pp)
-        base_convert(ctx, p.moddown, pc.u() + (size_t)pp * p.K * N, conv.u() + (size_t)pp * p.L * N, true);
+    base_convert_batch(ctx, p.moddown_b[polys], pc.u(), conv.u(), true);
     ntt_forward(ctx, conv.u(), conv.u(), p.ntt_conv[polys]);
     moddown_finish(ctx, level, acc, p.W, conv.u(), addend, addend_stride, addend_polys, out, out_stride, polys);
 }

@@ -14,6 +14,8 @@ struct KsPlan {                       // everything a key switch at one level ne
     NttPlan ntt_digits;               // all converted (non-own) limbs of the digit buffer, in place
     NttPlan intt_p[3];                // [polys]: P limbs of acc -> scratch [polys][K][N]
     BaseConvPlan moddown;             // P -> Q_0..Q_level (centered), one polynomial
+    BaseConvBatch modup_all;          // every digit in one launch
+    BaseConvBatch moddown_b[3];       // [polys]
     NttPlan ntt_conv[3];              // [polys]: conv [polys][L][N] in place
 };
 

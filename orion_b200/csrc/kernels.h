@@ -29,6 +29,17 @@ struct BaseConvPlan { const BaseConv* bc = nullptr; const LimbDesc* out_off = nu
 BaseConvPlan make_baseconv_plan(Context& c, const std::vector<int>& src, const std::vector<int>& dst,
                                 const std::vector<int>& out_off);
 void base_convert(Context& c, const BaseConvPlan& p, const u64* in, u64* out, bool centered);
+// several conversions in one launch (all digits of a ModUp, both polynomials of a ModDown): conversion z reads its
+// sources at in + (in_off[z] + i)*N and writes destination d at out + (out_base[z] + plan.out_off[d])*N.
+struct BcDev {
+    int ns, nd, in_off, out_base;
+    const int* src_mod; const int* dst_mod; const LimbDesc* out_off;
+    const ulonglong2* inv; const u64* mat; const u64* negvq; const u64* half_src; const u64* half_dst;
+};
+struct BaseConvBatch { const BcDev* dev = nullptr; int n = 0; size_t smem = 0; };
+BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& plans, const std::vector<int>& in_off,
+                                  const std::vector<int>& out_base);
+void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered);
 
 // ---- key-switch inner product ----
 // acc[c][t][x] = sum_j digit_j[t][x] * evk[j][c][chain(t)][x]  (evk in Montgomery form, full-chain layout).

@@ -58,6 +58,69 @@ baseconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, int ns
     }
 }
 
+
+// Batched base conversion: one CTA column per conversion (blockIdx.y), every thread converts one coefficient to ALL
+// destination limbs.  The conversion's constants are staged once per CTA in shared memory, so the inner loop is
+// ns MACs + 1 REDC per output with no dependent global loads.
+constexpr int BC_TPB = 128;
+template <bool CENTERED>
+__global__ void __launch_bounds__(BC_TPB)
+baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
+                      const ModConst* __restrict__ mc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const BcDev d = descs[blockIdx.y];
+    const int ns = d.ns, nd = d.nd;
+    u64* s_mat = (u64*)smem_raw;                       // [ns][nd]
+    u64* s_neg = s_mat + ns * nd;                      // [nd][ns+1]
+    u64* s_dq = s_neg + nd * (ns + 1);                 // [nd]
+    u64* s_dqi = s_dq + nd;                            // [nd]
+    u64* s_dh = s_dqi + nd;                            // [nd]
+    u64* s_sq = s_dh + nd;                             // [ns]
+    u64* s_sh = s_sq + ns;                             // [ns]
+    double* s_sqd = (double*)(s_sh + ns);              // [ns]
+    ulonglong2* s_inv = (ulonglong2*)(s_sqd + ns + (ns & 1));   // [ns], 16-byte aligned
+    int* s_off = (int*)(s_inv + ns);                   // [nd]
+    for (int i = threadIdx.x; i < ns * nd; i += BC_TPB) s_mat[i] = d.mat[i];
+    for (int i = threadIdx.x; i < nd * (ns + 1); i += BC_TPB) s_neg[i] = d.negvq[i];
+    for (int i = threadIdx.x; i < nd; i += BC_TPB) {
+        const ModConst& m = mc[d.dst_mod[i]];
+        s_dq[i] = m.q; s_dqi[i] = m.qinv_neg; s_dh[i] = CENTERED ? d.half_dst[i] : 0;
+        s_off[i] = d.out_base + (int)d.out_off[i].in_off;
+    }
+    for (int i = threadIdx.x; i < ns; i += BC_TPB) {
+        const ModConst& m = mc[d.src_mod[i]];
+        s_sq[i] = m.q; s_sqd[i] = m.qd; s_inv[i] = d.inv[i]; s_sh[i] = CENTERED ? d.half_src[i] : 0;
+    }
+    __syncthreads();
+    const int x = blockIdx.x * BC_TPB + threadIdx.x;
+    u64 y[MAX_NS];
+    double vf = 0.0;
+#pragma unroll
+    for (int i = 0; i < MAX_NS; ++i) {
+        if (i < ns) {
+            const u64 q = s_sq[i];
+            u64 xi = in[(size_t)(d.in_off + i) * N + x];
+            if (CENTERED) xi = add_mod(xi, s_sh[i], q);
+            const ulonglong2 w = s_inv[i];
+            y[i] = shoup_mul(xi, w.x, w.y, q);
+            vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(y[i]), s_sqd[i]));
+        }
+    }
+    const u64 v = (ns == 1 && !CENTERED) ? 0 : (u64)vf;
+#pragma unroll 2
+    for (int t = 0; t < nd; ++t) {
+        const u64 q = s_dq[t];
+        u64 hi = 0, lo = 0;
+#pragma unroll
+        for (int i = 0; i < MAX_NS; ++i)
+            if (i < ns) mac128(hi, lo, y[i], s_mat[i * nd + t], q);
+        u64 r = mont_redc(hi, lo, q, s_dqi[t]);
+        r = add_mod(r, s_neg[t * (ns + 1) + v], q);
+        if (CENTERED) r = sub_mod(r, s_dh[t], q);
+        out[(size_t)s_off[t] * N + x] = r;
+    }
+}
+
 // acc[c][t][x] (+)= sum_j dig_j[t][x] * evk[j][c][chain(t)][x]   (evk Montgomery form)
 template <bool GATHER, bool ACCUM>
 __global__ void __launch_bounds__(TPB)
@@ -159,6 +222,34 @@ void base_convert(Context& c, const BaseConvPlan& p, const u64* in, u64* out, bo
         OB_LAUNCH((baseconv_kernel<false>), grid, TPB, 0, stream(), in, out, c.N, b.ns, b.nd, b.src_mod.as<int>(),
                   b.dst_mod.as<int>(), p.out_off, b.inv.as<ulonglong2>(), b.mat.u(), b.negvq.u(), b.half_src.u(),
                   b.half_dst.u(), c.dmc());
+}
+
+BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& plans, const std::vector<int>& in_off,
+                                  const std::vector<int>& out_base) {
+    BaseConvBatch b; b.n = (int)plans.size();
+    std::vector<BcDev> h(plans.size());
+    for (size_t z = 0; z < plans.size(); ++z) {
+        const BaseConv& bc = *plans[z].bc;
+        h[z] = BcDev{bc.ns, bc.nd, in_off[z], out_base[z], bc.src_mod.as<int>(), bc.dst_mod.as<int>(), plans[z].out_off,
+                     bc.inv.as<ulonglong2>(), bc.mat.u(), bc.negvq.u(), bc.half_src.u(), bc.half_dst.u()};
+        const size_t ns = bc.ns, nd = bc.nd;
+        const size_t sm = 8 * (ns * nd + nd * (ns + 1) + 3 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 4 * nd + 16;
+        b.smem = std::max(b.smem, sm);
+    }
+    auto buf = std::make_unique<DevBuf>(h.size() * sizeof(BcDev));
+    OB_CUDA(cudaMemcpyAsync(buf->p, h.data(), h.size() * sizeof(BcDev), cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    b.dev = buf->as<BcDev>();
+    c.misc.push_back(std::move(buf));
+    return b;
+}
+
+void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered) {
+    if (b.n == 0) return;
+    OB_CHECK(b.smem <= 48 * 1024, "base conversion tables exceed the static shared-memory window");
+    dim3 grid(c.N / BC_TPB, b.n);
+    if (centered) OB_LAUNCH((baseconv_batch_kernel<true>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc());
+    else OB_LAUNCH((baseconv_batch_kernel<false>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc());
 }
 
 void ks_inner_product(Context& c, int level, const u64* c1_ntt, const u64* digits, const u64* evk,

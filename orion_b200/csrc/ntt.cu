@@ -100,11 +100,12 @@ __host__ __device__ inline Rounds split_rounds(int bits) {
 // One pass.  STRIDED: tile = 2^nbits rows x C cols, transformed bits are local bits [logC, LOG_E).
 //            contiguous: tile = 2^LOG_E consecutive words, transformed bits are local bits [0, nbits).
 // FWD walks the transformed bits downwards, INV upwards.  FINAL: normalise (and scale by N^-1 for INV).
-template <int LOG_E, bool STRIDED, bool FWD, bool FINAL>
+template <int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
 __global__ void __launch_bounds__(1 << (LOG_E - 3))
 ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
          const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all,
-         const ulonglong2* __restrict__ ninv_all, int logN, int nbits) {
+         const ulonglong2* __restrict__ ninv_all, int logN) {
+    constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
     __shared__ u64 sm[1 << LOG_E];
     const int tid = threadIdx.x;
     const LimbDesc ld = limbs[blockIdx.y];
@@ -123,10 +124,11 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
         return tile_base + li;
     };
 
-    const Rounds rd = split_rounds(nbits);
+    constexpr int NR = (NBITS + 2) / 3, RBASE = NBITS / NR, REXTRA = NBITS % NR;
     int done = 0;
-    for (int r = 0; r < rd.n; ++r) {
-        const int nb = rd.nb[r];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const int nb = RBASE + (r < REXTRA ? 1 : 0);
         const int G = 8 >> nb;
         const int pos = FWD ? lo_bit + nbits - done - nb : lo_bit + done;   // lowest bit of this round
         const int ptop = pos + nb - 1;
@@ -152,7 +154,7 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
             if (nb == 3) inv_radix<3>(v, tw, twb, q); else if (nb == 2) inv_radix<2>(v, tw, twb, q); else inv_radix<1>(v, tw, twb, q);
         }
         done += nb;
-        if (r == rd.n - 1) {
+        if (r == NR - 1) {
             if (FINAL) {
                 if (FWD) {
 #pragma unroll
@@ -185,27 +187,35 @@ NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
     return p;
 }
 
+#define OB_NTT_STRIDED(S1, FWD, FINAL, ...) \
+    OB_LAUNCH((ntt_pass<LOG_E_STRIDED, S1, true, FWD, FINAL>), g1, 1 << (LOG_E_STRIDED - 3), 0, stream(), __VA_ARGS__)
+#define OB_NTT_STRIDED_SWITCH(FWD, FINAL, ...) \
+    switch (s1) { \
+        case 4: OB_NTT_STRIDED(4, FWD, FINAL, __VA_ARGS__); break; \
+        case 5: OB_NTT_STRIDED(5, FWD, FINAL, __VA_ARGS__); break; \
+        case 6: OB_NTT_STRIDED(6, FWD, FINAL, __VA_ARGS__); break; \
+        case 7: OB_NTT_STRIDED(7, FWD, FINAL, __VA_ARGS__); break; \
+        case 8: OB_NTT_STRIDED(8, FWD, FINAL, __VA_ARGS__); break; \
+        case 9: OB_NTT_STRIDED(9, FWD, FINAL, __VA_ARGS__); break; \
+        default: OB_FATAL("unsupported logN"); }
+
 // Batched forward NTT: limb i is read at in + in_off*N and written at out + out_off*N.
 void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
-    OB_CHECK(c.logN >= 12, "logN >= 12 required");
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
-    OB_LAUNCH((ntt_pass<LOG_E_STRIDED, true, true, false>), g1, 1 << (LOG_E_STRIDED - 3), 0, stream(),
-              in, out, p.first, c.dmc(), c.tw_fwd(), c.d_ninv.as<ulonglong2>(), c.logN, s1);
-    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, false, true, true>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
-              (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.d_ninv.as<ulonglong2>(), c.logN, K2_BITS);
+    OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
+    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, true, true>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
+              (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
 }
 
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
-    OB_CHECK(c.logN >= 12, "logN >= 12 required");
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
-    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, false, false, false>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
-              in, out, p.first, c.dmc(), c.tw_inv(), c.d_ninv.as<ulonglong2>(), c.logN, K2_BITS);
-    OB_LAUNCH((ntt_pass<LOG_E_STRIDED, true, false, true>), g1, 1 << (LOG_E_STRIDED - 3), 0, stream(),
-              (const u64*)out, out, p.second, c.dmc(), c.tw_inv(), c.d_ninv.as<ulonglong2>(), c.logN, s1);
+    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, false, false>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
+              in, out, p.first, c.dmc(), c.tw_inv(), c.d_ninv.as<ulonglong2>(), c.logN);
+    OB_NTT_STRIDED_SWITCH(false, true, (const u64*)out, out, p.second, c.dmc(), c.tw_inv(), c.d_ninv.as<ulonglong2>(), c.logN)
 }
 
 }  // namespace ob
