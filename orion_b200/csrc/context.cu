@@ -151,6 +151,7 @@ ModConst make_modconst(u64 q) {
     m.r1 = (u64)((((u128)1) << 64) % q); m.r1_sh = shoup_companion(m.r1, q);
     m.r2 = mulmod_u64(m.r1, m.r1, q);    m.r2_sh = shoup_companion(m.r2, q);
     m.qd = (double)q;
+    m.one_sh = shoup_companion(1, q);
     return m;
 }
 

@@ -63,7 +63,7 @@ baseconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, int ns
 // destination limbs.  The conversion's constants are staged once per CTA in shared memory, so the inner loop is
 // ns MACs + 1 REDC per output with no dependent global loads.
 constexpr int BC_TPB = 128;
-template <bool CENTERED>
+template <bool CENTERED, int NS>      // NS = compile-time bound on the source-limb count of every conversion in the batch
 __global__ void __launch_bounds__(BC_TPB)
 baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                       const ModConst* __restrict__ mc) {
@@ -93,10 +93,10 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     }
     __syncthreads();
     const int x = blockIdx.x * BC_TPB + threadIdx.x;
-    u64 y[MAX_NS];
+    u64 y[NS];
     double vf = 0.0;
 #pragma unroll
-    for (int i = 0; i < MAX_NS; ++i) {
+    for (int i = 0; i < NS; ++i) {
         if (i < ns) {
             const u64 q = s_sq[i];
             u64 xi = in[(size_t)(d.in_off + i) * N + x];
@@ -112,7 +112,7 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
         const u64 q = s_dq[t];
         u64 hi = 0, lo = 0;
 #pragma unroll
-        for (int i = 0; i < MAX_NS; ++i)
+        for (int i = 0; i < NS; ++i)
             if (i < ns) mac128(hi, lo, y[i], s_mat[i * nd + t], q);
         u64 r = mont_redc(hi, lo, q, s_dqi[t]);
         r = add_mod(r, s_neg[t * (ns + 1) + v], q);
@@ -235,6 +235,7 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
         const size_t ns = bc.ns, nd = bc.nd;
         const size_t sm = 8 * (ns * nd + nd * (ns + 1) + 3 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 4 * nd + 16;
         b.smem = std::max(b.smem, sm);
+        b.max_ns = std::max(b.max_ns, bc.ns);
     }
     auto buf = std::make_unique<DevBuf>(h.size() * sizeof(BcDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, h.data(), h.size() * sizeof(BcDev), cudaMemcpyHostToDevice, stream()));
@@ -248,8 +249,11 @@ void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* 
     if (b.n == 0) return;
     OB_CHECK(b.smem <= 48 * 1024, "base conversion tables exceed the static shared-memory window");
     dim3 grid(c.N / BC_TPB, b.n);
-    if (centered) OB_LAUNCH((baseconv_batch_kernel<true>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc());
-    else OB_LAUNCH((baseconv_batch_kernel<false>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc());
+#define OB_BC(NSV) do { if (centered) OB_LAUNCH((baseconv_batch_kernel<true, NSV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); \
+                       else OB_LAUNCH((baseconv_batch_kernel<false, NSV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+    if (b.max_ns <= 1) OB_BC(1); else if (b.max_ns <= 2) OB_BC(2); else if (b.max_ns <= 3) OB_BC(3); else if (b.max_ns <= 4) OB_BC(4);
+    else if (b.max_ns <= 6) OB_BC(6); else if (b.max_ns <= 8) OB_BC(8); else OB_BC(MAX_NS);
+#undef OB_BC
 }
 
 void ks_inner_product(Context& c, int level, const u64* c1_ntt, const u64* digits, const u64* evk,

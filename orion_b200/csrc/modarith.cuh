@@ -30,7 +30,7 @@ struct ModConst {
     int bits;      // bit length of q
     int pad;
     double qd;     // (double) q
-    u64 pad2;
+    u64 one_sh;    // floor(2^64/q): Shoup companion of 1 (reduces any 64-bit value to [0,2q))
 };
 
 #ifdef __CUDACC__
