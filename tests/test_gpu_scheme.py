@@ -235,3 +235,38 @@ def test_polynomial_evaluation(orc, b200lib):
     out = B.EvaluatePolynomial(ct, pm, 1 << 40)
     assert np.max(np.abs(dec(out) - np.polynomial.polynomial.polyval(x, c32))) < 1e-5
     B.DeleteScheme()
+
+
+@pytest.mark.parametrize("num_slots", [2048, 256])
+def test_bootstrap(orc, b200lib, num_slots):
+    """Bootstrap contract (lattigo/bootstrapper.go:61-80): any input level -> top level, default scale, same values."""
+    from orion_b200.bindings import B200Library
+    B = B200Library()
+    B.B200_SetSeed(11)
+    logq = [55, 40, 40, 40, 40]
+    B.NewScheme(12, logq, [56, 56], 40, 64, "standard", "", "none")
+    B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey()
+    B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor(); B.NewEvaluator()
+    B.NewBootstrapper([61, 61, 61, 61], num_slots)
+    rng = np.random.default_rng(8)
+    slots = 2048
+    base = rng.uniform(-1, 1, num_slots)
+    x = np.tile(base, slots // num_slots)                 # sparse packing == a periodic full-slot vector
+    pt = B.B200_EncodeF64(x, slots, 1, float(1 << 40))
+    ct = B.Encrypt(pt)
+    out = B.Bootstrap(ct, num_slots)
+    assert B.GetCiphertextLevel(out) == len(logq) - 1
+    assert B.GetCiphertextScale(out) == 1 << 40
+    p = B.Decrypt(out)
+    re, im = np.empty(slots), np.empty(slots)
+    B.B200_DecodeF64(p, re, im)
+    err = np.max(np.abs(re - x))
+    assert err < 2e-4, err
+    assert np.max(np.abs(im)) < 2e-4
+    # the refreshed ciphertext is usable: one multiplication + rescale
+    sq = B.Rescale(B.MulRelinCiphertextNew(out, out))
+    p2 = B.Decrypt(sq)
+    B.B200_DecodeF64(p2, re, im)
+    assert np.max(np.abs(re - x * x)) < 5e-4
+    B.DeleteBootstrappers()
+    B.DeleteScheme()
