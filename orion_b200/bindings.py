@@ -213,6 +213,9 @@ class B200Library:
         self.arithmeticoperator_handle = None       # attribute the drifted Python layer passes around (PY/evaluator.py:36-40)
         for name, (spec, res) in SCHEME_SIGNATURES.items():
             setattr(self, name, B200Function(getattr(self.lib, name), spec, res))   # a missing export fails loudly here
+        # PY/poly_evaluator.py:23 calls GenerateChebyshev(coeffs, len(coeffs)) (heongpu-adapter signature): accept both
+        cheb = self.GenerateChebyshev
+        self.GenerateChebyshev = lambda coeffs, *_n: cheb(coeffs)
         B200Function.free = self.lib.FreeCArray
         self.lib.FreeCArray.argtypes = [c_vp]
         self.lib.FreeCArray.restype = None
@@ -222,6 +225,11 @@ class B200Library:
         self.NewScheme(orion_params.get_logn(), orion_params.get_logq(), orion_params.get_logp(),
                        orion_params.get_logscale(), orion_params.get_hamming_weight(), orion_params.get_ringtype(),
                        orion_params.get_keys_path(), orion_params.get_io_mode())
+
+    # host-only: composite minimax sign polynomials (lattigo/polyeval.go:91-167); same arguments, flat list out
+    def GenerateMinimaxSignCoeffs(self, degrees, prec=128, logalpha=12, logerr=12, debug=0):
+        from .minimax import generate_minimax_sign_coeffs
+        return generate_minimax_sign_coeffs(list(degrees), prec, logalpha, logerr, bool(debug))
 
     # extras of the heongpu adapter used by the backend-agnostic wrappers
     def _ModDropCiphertext(self, _op_handle, ct, _opts=None):

@@ -22,7 +22,7 @@ class Trace:
 
     def values(self, key, rng):
         a = self.payload[key]
-        if self.meta["payloads"] == "full" or a.dtype != np.int64:
+        if a.dtype != np.int64:
             return a
         n = int(a[0])
         return (rng.standard_normal(n) * 0.05).astype(np.float32)       # synthetic payload of the recorded size
@@ -102,9 +102,19 @@ class Replayer:
     def setup(self):
         """init_scheme + compile: everything up to (not including) the encode of the input."""
         self.run(0, self.t.n_compile)
+        self._snap = (dict(self.ct), dict(self.pt))
 
     def infer(self):
-        """One encrypted inference: encode + encrypt the input, net(ct), decrypt + decode.  Returns the decoded slots."""
+        """One encrypted inference: encode + encrypt the input, net(ct), decrypt + decode.  Returns the decoded slots.
+        Repeatable: handles created by a previous inference are released first."""
+        ct0, pt0 = self._snap
+        for k, v in list(self.ct.items()):
+            if k not in ct0 or ct0[k] != v:
+                self.B.DeleteCiphertext(v)
+        for k, v in list(self.pt.items()):
+            if k not in pt0 or pt0[k] != v:
+                self.B.DeletePlaintext(v)
+        self.ct, self.pt = dict(ct0), dict(pt0)
         self.run(self.t.n_compile, len(self.t.ops))
         return self.output
 

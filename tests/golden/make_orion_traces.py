@@ -37,6 +37,23 @@ def stub_missing_modules():
         sys.modules["matplotlib"].pyplot = sys.modules.get("matplotlib.pyplot")
 
 
+def patch_scipy_for_torch_indices():
+    """The reference indexes scipy sparse matrices with torch tensors (orion/core/packing.py:94,100); the scipy in this
+    image only accepts numpy indices.  Convert at the scipy boundary instead of touching the reference."""
+    import scipy.sparse as sp
+    import torch
+
+    def conv(k):
+        if isinstance(k, tuple):
+            return tuple(conv(x) for x in k)
+        return k.numpy() if isinstance(k, torch.Tensor) else k
+
+    for cls in (sp.lil_matrix, sp.csc_matrix, sp.csr_matrix):
+        g, st = cls.__getitem__, cls.__setitem__
+        cls.__getitem__ = (lambda g: lambda self, k: g(self, conv(k)))(g)
+        cls.__setitem__ = (lambda st: lambda self, k, v: st(self, conv(k), v.numpy() if isinstance(v, torch.Tensor) else v))(st)
+
+
 class SymbolicBackend:
     """Tracks metadata only.  Scale / level rules are those of include/orion_b200_scheme.h (= the Go shim's)."""
 
@@ -70,7 +87,7 @@ class SymbolicBackend:
     def _store(self, arr, dtype=np.float32):
         key = "p%d" % len(self.payload)
         a = np.asarray(arr, dtype=dtype)
-        self.payload[key] = a if self.keep else np.array([a.size], dtype=np.int64)
+        self.payload[key] = a if (self.keep or a.size <= 512) else np.array([a.size], dtype=np.int64)   # polynomials are always kept
         return key
 
     # ---- scheme ----
@@ -285,6 +302,7 @@ def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "mlp"
     keep = name != "resnet20" and "--structure-only" not in sys.argv
     stub_missing_modules()
+    patch_scipy_for_torch_indices()
     sys.path.insert(0, REF)
     import torch
     import orion
@@ -320,7 +338,8 @@ def main():
                 output_ct_ids=[int(i) for i in out_ids], payloads="full" if keep else "sizes",
                 Q=[int(q) for q in sb.Q], P=[int(p) for p in sb.P],
                 clear_output=clear.tolist(), n_ops=len(sb.ops))
-    base = os.path.join(ROOT, "tests", "golden", "trace_" + name)
+    suffix = "" if cfg["ckks_params"]["LogN"] == yaml.safe_load(open(cfg_path))["ckks_params"]["LogN"] else "_logn%d" % cfg["ckks_params"]["LogN"]
+    base = os.path.join(ROOT, "tests", "golden", "trace_" + name + suffix)
     def plain(o):
         if isinstance(o, (list, tuple)):
             return [plain(v) for v in o]

@@ -28,3 +28,15 @@ def test_mlp_encrypted_inference_matches_cleartext(b200lib):
     assert int(np.argmax(fhe)) == int(np.argmax(clear))
     assert np.max(np.abs(clear - fhe)) < 1e-2
     assert res["counts"]["EvaluateLinearTransform"] == 3 and res["counts"]["MulRelinCiphertextNew"] == 2
+
+
+def test_resnet20_trace_replays_with_bootstrapping(b200lib):
+    """ResNet-20 as shipped (configs/resnet.yml: logN=13, 33 Q-limbs, boot LogP 8x61): the reference's exact call
+    sequence (147 linear transforms, 138 polynomial evaluations, 28 bootstraps) on synthetic payloads of the recorded
+    shapes.  Checks the structural contract end to end: every op's level budget holds and the output is finite."""
+    res = run_trace("resnet20")
+    c = res["counts"]
+    assert c["EvaluateLinearTransform"] == 147 and c["EvaluatePolynomial"] == 138 and c["Bootstrap"] == 28
+    out = res["output"]
+    assert out is not None and np.all(np.isfinite(out))
+    print("resnet20 logN=13: setup %.1f s, one encrypted inference %.2f s" % (res["setup_s"], res["infer_s"]))
