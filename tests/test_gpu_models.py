@@ -40,3 +40,12 @@ def test_resnet20_trace_replays_with_bootstrapping(b200lib):
     out = res["output"]
     assert out is not None and np.all(np.isfinite(out))
     print("resnet20 logN=13: setup %.1f s, one encrypted inference %.2f s" % (res["setup_s"], res["infer_s"]))
+
+
+def test_lola_encrypted_inference_matches_cleartext(b200lib):
+    """LoLA CNN with configs/lola2.yml (logN=14, 7+2 limbs, Standard ring): same MAE gate as the reference's MLP test."""
+    res = run_trace("lola")
+    clear = np.array(res["meta"]["clear_output"])
+    fhe = res["output"][: len(clear)]
+    assert float(np.mean(np.abs(clear - fhe))) < 0.005
+    assert int(np.argmax(fhe)) == int(np.argmax(clear))
