@@ -151,6 +151,7 @@ ModConst make_modconst(u64 q) {
     m.r1 = (u64)((((u128)1) << 64) % q); m.r1_sh = shoup_companion(m.r1, q);
     m.r2 = mulmod_u64(m.r1, m.r1, q);    m.r2_sh = shoup_companion(m.r2, q);
     m.qd = (double)q;
+    m.qinv_d = 1.0 / (double)q;
     m.one_sh = shoup_companion(1, q);
     return m;
 }
@@ -180,6 +181,7 @@ Context::Context(int logN_, const std::vector<u64>& Q, const std::vector<u64>& P
     OB_CHECK(nmod <= 64, "at most 64 moduli");
     mod = Q; mod.insert(mod.end(), P.begin(), P.end());
     std::vector<ulonglong2> twf((size_t)nmod * N), twi((size_t)nmod * N), ninv(nmod);
+    std::vector<double> twdf((size_t)nmod * N), twdi((size_t)nmod * N);
     for (int m = 0; m < nmod; ++m) {
         u64 q = mod[m];
         OB_CHECK((q - 1) % (2ull * N) == 0, "modulus is not 1 mod 2N");
@@ -191,12 +193,14 @@ Context::Context(int logN_, const std::vector<u64>& Q, const std::vector<u64>& P
             uint32_t j = bitrev_u32((uint32_t)i, logN);
             twf[(size_t)m * N + j] = make_ulonglong2(pf, shoup_companion(pf, q));
             twi[(size_t)m * N + j] = make_ulonglong2(pi, shoup_companion(pi, q));
+            twdf[(size_t)m * N + j] = (double)pf; twdi[(size_t)m * N + j] = (double)pi;   // exact below 2^53
             pf = mulmod_u64(pf, ps, q); pi = mulmod_u64(pi, psi_inv, q);
         }
         u64 ni = invmod_u64((u64)N % q, q);
         ninv[m] = make_ulonglong2(ni, shoup_companion(ni, q));
     }
     upload(d_mc, mc); upload(d_tw_fwd, twf); upload(d_tw_inv, twi); upload(d_ninv, ninv);
+    upload(d_twd_fwd, twdf); upload(d_twd_inv, twdi);
 
     std::vector<ulonglong2> pinv(nQ), pmodq(nQ), qlinv((size_t)nQ * nQ);
     for (int i = 0; i < nQ; ++i) {

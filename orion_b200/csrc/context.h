@@ -38,6 +38,8 @@ struct Context {
     DevBuf d_mc;        // ModConst[nmod]
     DevBuf d_tw_fwd;    // ulonglong2[nmod][N]  (psi^bitrev(i), shoup)
     DevBuf d_tw_inv;    // ulonglong2[nmod][N]  (psi^-bitrev(i), shoup)
+    DevBuf d_twd_fwd;   // double[nmod][N]      the same twiddles as exact doubles (FP64 butterfly path, primes <= 46 bits)
+    DevBuf d_twd_inv;   // double[nmod][N]
     DevBuf d_ninv;      // ulonglong2[nmod]     (N^-1, shoup)
     DevBuf d_pinv;      // ulonglong2[nQ]       (P^-1 mod q_i, shoup)          ModDown
     DevBuf d_qlinv;     // ulonglong2[nQ][nQ]   [l][i] = q_l^-1 mod q_i, shoup  rescale
@@ -51,6 +53,8 @@ struct Context {
     const ModConst* dmc() const { return d_mc.as<ModConst>(); }
     const ulonglong2* tw_fwd() const { return d_tw_fwd.as<ulonglong2>(); }
     const ulonglong2* tw_inv() const { return d_tw_inv.as<ulonglong2>(); }
+    const double* twd_fwd() const { return d_twd_fwd.as<double>(); }
+    const double* twd_inv() const { return d_twd_inv.as<double>(); }
 
     // cached device-side descriptors
     const LimbDesc* limb_list(const std::vector<LimbDesc>& v);

@@ -31,6 +31,7 @@ struct ModConst {
     int pad;
     double qd;     // (double) q
     u64 one_sh;    // floor(2^64/q): Shoup companion of 1 (reduces any 64-bit value to [0,2q))
+    double qinv_d; // 1.0 / (double) q, correctly rounded (FP64 butterfly path)
 };
 
 #ifdef __CUDACC__

@@ -31,24 +31,87 @@ __device__ __forceinline__ int insert_bits(int x, int pos, int nb, int v) {
 // bijection on the low 4 bits: keeps 64-bit shared-memory accesses conflict-free for all round shapes
 __device__ __forceinline__ int swz(int li) { return li ^ ((li >> 4) & 3) ^ (((li >> 5) & 3) << 2); }
 
-__device__ __forceinline__ void ct_bfly(u64& a, u64& b, ulonglong2 w, u64 q, u64 q2) {
-    u64 x = a >= q2 ? a - q2 : a;                 // [0,2q)
-    u64 v = shoup_lazy(b, w.x, w.y, q);           // [0,2q)
-    a = x + v;                                    // [0,4q)
-    b = x - v + q2;                               // (0,4q)
-}
-__device__ __forceinline__ void gs_bfly(u64& a, u64& b, ulonglong2 w, u64 q, u64 q2) {
-    u64 s = a + b;                                // [0,4q)
-    u64 d = a - b + q2;                           // (0,4q)
-    a = s >= q2 ? s - q2 : s;                     // [0,2q)
-    b = shoup_lazy(d, w.x, w.y, q);               // [0,2q)
-}
+// ---- arithmetic policies ------------------------------------------------------------------------------------
+// ArithInt : Harvey lazy butterflies on u64 with Shoup twiddles (any prime < 2^62).  6 IMAD.WIDE + 4 IMAD per
+//            butterfly; IMAD.WIDE issues at 32 lanes/clk/SM on B200 (tools/ubench_int.cu), so this path tops out
+//            at 2.8 butterflies/clk/SM (tools/ubench_bfly.cu).
+// ArithF64 : primes of at most F64_MAX_BITS bits.  Residues are carried as exact integers in doubles, in a signed
+//            lazy range; x*w mod q is  h = x*w, l = fma(x,w,-h), t = rint(h/q), r = fma(-t,q,h) + l  (6 DFMA-class
+//            ops, all exact -- see the bounds below) and B200 issues DFMA at 64 lanes/clk/SM, which measures
+//            6.2 butterflies/clk/SM.  Results are normalised to [0,q) on the way out, so both paths produce the
+//            same words.
+//   bounds (q < 2^46, logN <= 17): forward values grow by <= 0.7q per stage -> |v| < 13q < 2^49.7 (no reduction
+//   needed); rint() via the 1.5*2^52 trick needs |h/q| < 2^51; h - t*q is an integer of magnitude < q + ulp(h)/2
+//   < 2^47, so the fma and the final add are exact.  The inverse doubles the sum path each stage, so every value
+//   is re-centred at the end of a radix-8 round (|v| <= 8 * 0.7q inside a round).
+constexpr int F64_MAX_BITS = 46;
+constexpr double F64_MAGIC = 6755399441055744.0;            // 1.5 * 2^52
+constexpr unsigned long long F64_EXP52 = 0x4330000000000000ull;   // bit pattern of 2^52
+
+struct ArithInt {
+    typedef u64 T;
+    typedef ulonglong2 TW;
+    u64 q, q2;
+    __device__ __forceinline__ explicit ArithInt(const ModConst& m) : q(m.q), q2(2 * m.q) {}
+    __device__ __forceinline__ T from_word(u64 x) const { return x; }          // normalised input word
+    __device__ __forceinline__ T from_raw(u64 x) const { return x; }           // inter-pass / shared-memory word
+    __device__ __forceinline__ u64 to_raw(T x) const { return x; }
+    __device__ __forceinline__ TW ldtw(const TW* p) const { return __ldg(p); }
+    __device__ __forceinline__ void ct(T& a, T& b, TW w) const {
+        u64 x = a >= q2 ? a - q2 : a;                 // [0,2q)
+        u64 v = shoup_lazy(b, w.x, w.y, q);           // [0,2q)
+        a = x + v;                                    // [0,4q)
+        b = x - v + q2;                               // (0,4q)
+    }
+    __device__ __forceinline__ void gs(T& a, T& b, TW w) const {
+        u64 s = a + b;                                // [0,4q)
+        u64 d = a - b + q2;                           // (0,4q)
+        a = s >= q2 ? s - q2 : s;                     // [0,2q)
+        b = shoup_lazy(d, w.x, w.y, q);               // [0,2q)
+    }
+    __device__ __forceinline__ void recentre(T&) const {}
+    __device__ __forceinline__ u64 final_fwd(T x) const { x = x >= q2 ? x - q2 : x; return x >= q ? x - q : x; }
+    __device__ __forceinline__ u64 final_inv(T x, ulonglong2 ni) const { return shoup_mul(x, ni.x, ni.y, q); }
+};
+
+struct ArithF64 {
+    typedef double T;
+    typedef double TW;
+    double q, qinv;
+    __device__ __forceinline__ explicit ArithF64(const ModConst& m) : q(m.qd), qinv(m.qinv_d) {}
+    __device__ __forceinline__ T from_word(u64 x) const { return __dsub_rn(__longlong_as_double(x | F64_EXP52), 4503599627370496.0); }
+    __device__ __forceinline__ T from_raw(u64 x) const { return __longlong_as_double(x); }
+    __device__ __forceinline__ u64 to_raw(T x) const { return (u64)__double_as_longlong(x); }
+    __device__ __forceinline__ TW ldtw(const TW* p) const { return __ldg(p); }
+    __device__ __forceinline__ T mulmod(T x, T w) const {                     // centred residue of x*w, |r| <= 0.7q
+        const double h = __dmul_rn(x, w), l = __fma_rn(x, w, -h);
+        const double t = __dsub_rn(__fma_rn(h, qinv, F64_MAGIC), F64_MAGIC);
+        return __dadd_rn(__fma_rn(-t, q, h), l);
+    }
+    __device__ __forceinline__ void ct(T& a, T& b, TW w) const {
+        const double r = mulmod(b, w);
+        b = __dsub_rn(a, r); a = __dadd_rn(a, r);
+    }
+    __device__ __forceinline__ void gs(T& a, T& b, TW w) const {
+        const double s = __dadd_rn(a, b), d = __dsub_rn(a, b);
+        a = s; b = mulmod(d, w);
+    }
+    __device__ __forceinline__ void recentre(T& x) const {
+        const double t = __dsub_rn(__fma_rn(x, qinv, F64_MAGIC), F64_MAGIC);
+        x = __fma_rn(-t, q, x);
+    }
+    __device__ __forceinline__ u64 to_word(T x) const {                        // x integer in (-q, q) -> [0,q)
+        x = x < 0.0 ? __dadd_rn(x, q) : x;
+        return (u64)__double_as_longlong(__dadd_rn(x, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+    }
+    __device__ __forceinline__ u64 final_fwd(T x) const { recentre(x); return to_word(x); }
+    __device__ __forceinline__ u64 final_inv(T x, ulonglong2 ni) const { return to_word(mulmod(x, from_word(ni.x))); }
+};
 
 // forward radix-2^NB on 8>>NB independent groups held in v[]
-template <int NB>
-__device__ __forceinline__ void fwd_radix(u64 (&v)[8], const ulonglong2* __restrict__ tw, const int (&twb)[8], u64 q) {
+template <int NB, class A>
+__device__ __forceinline__ void fwd_radix(const A& ar, typename A::T (&v)[8], const typename A::TW* __restrict__ tw, const int (&twb)[8]) {
     constexpr int G = 8 >> NB, R = 1 << NB;
-    const u64 q2 = 2 * q;
 #pragma unroll
     for (int i = 0; i < NB; ++i) {
         const int half = 1 << (NB - 1 - i);
@@ -56,21 +119,20 @@ __device__ __forceinline__ void fwd_radix(u64 (&v)[8], const ulonglong2* __restr
         for (int g = 0; g < G; ++g) {
 #pragma unroll
             for (int m = 0; m < (1 << i); ++m) {
-                ulonglong2 w = __ldg(&tw[(twb[g] << i) + m]);
+                const typename A::TW w = ar.ldtw(&tw[(twb[g] << i) + m]);
 #pragma unroll
                 for (int k0 = 0; k0 < half; ++k0) {
                     int a = g * R + m * 2 * half + k0;
-                    ct_bfly(v[a], v[a + half], w, q, q2);
+                    ar.ct(v[a], v[a + half], w);
                 }
             }
         }
     }
 }
 // inverse radix-2^NB (bits ascending); twb[] is the twiddle index at the TOP bit of the round
-template <int NB>
-__device__ __forceinline__ void inv_radix(u64 (&v)[8], const ulonglong2* __restrict__ tw, const int (&twb)[8], u64 q) {
+template <int NB, bool RECENTRE, class A>
+__device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[8], const typename A::TW* __restrict__ tw, const int (&twb)[8]) {
     constexpr int G = 8 >> NB, R = 1 << NB;
-    const u64 q2 = 2 * q;
 #pragma unroll
     for (int i = 0; i < NB; ++i) {
         const int half = 1 << i;
@@ -78,45 +140,36 @@ __device__ __forceinline__ void inv_radix(u64 (&v)[8], const ulonglong2* __restr
         for (int g = 0; g < G; ++g) {
 #pragma unroll
             for (int m = 0; m < (R >> (i + 1)); ++m) {
-                ulonglong2 w = __ldg(&tw[(twb[g] << (NB - 1 - i)) + m]);
+                const typename A::TW w = ar.ldtw(&tw[(twb[g] << (NB - 1 - i)) + m]);
 #pragma unroll
                 for (int k0 = 0; k0 < half; ++k0) {
                     int a = g * R + m * 2 * half + k0;
-                    gs_bfly(v[a], v[a + half], w, q, q2);
+                    ar.gs(v[a], v[a + half], w);
                 }
             }
         }
     }
-}
-
-struct Rounds { int n; int nb[4]; };
-__host__ __device__ inline Rounds split_rounds(int bits) {
-    Rounds r; r.n = (bits + 2) / 3;
-    int base = bits / r.n, extra = bits % r.n;
-    for (int i = 0; i < r.n; ++i) r.nb[i] = base + (i < extra ? 1 : 0);
-    return r;
+    if (RECENTRE) {      // only the sum outputs of the round's last stage can have grown (the others are fresh products)
+#pragma unroll
+        for (int g = 0; g < G; ++g)
+#pragma unroll
+            for (int k0 = 0; k0 < R / 2; ++k0) ar.recentre(v[g * R + k0]);
+    }
 }
 
 // One pass.  STRIDED: tile = 2^nbits rows x C cols, transformed bits are local bits [logC, LOG_E).
 //            contiguous: tile = 2^LOG_E consecutive words, transformed bits are local bits [0, nbits).
-// FWD walks the transformed bits downwards, INV upwards.  FINAL: normalise (and scale by N^-1 for INV).
-template <int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
-__global__ void __launch_bounds__(1 << (LOG_E - 3))
-ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
-         const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all,
-         const ulonglong2* __restrict__ ninv_all, int logN) {
+// FWD walks the transformed bits downwards, INV upwards.  Every transform is exactly two passes: the first one
+// (!FINAL) reads normalised words and leaves policy-specific lazy values, the second one (FINAL) normalises (and
+// scales by N^-1 for INV).
+template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
+__device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restrict__ src, u64* __restrict__ dst,
+                                         const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN) {
+    typedef typename A::T T;
     constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
-    __shared__ u64 sm[1 << LOG_E];
     const int tid = threadIdx.x;
-    const LimbDesc ld = limbs[blockIdx.y];
-    const int N = 1 << logN;
-    const u64 q = mc[ld.mod].q;
-    const ulonglong2* tw = tw_all + (size_t)ld.mod * N;
-    const u64* src = in + (size_t)ld.in_off * N;
-    u64* dst = out + (size_t)ld.out_off * N;
-
-    const int logC = STRIDED ? LOG_E - nbits : 0;
-    const int lo_bit = STRIDED ? logC : 0;               // lowest transformed local bit
+    constexpr int logC = STRIDED ? LOG_E - nbits : 0;
+    constexpr int lo_bit = STRIDED ? logC : 0;           // lowest transformed local bit
     const int TOP = STRIDED ? LOG_E - 1 : logN - 1;      // stage = TOP - local bit
     const int tile_base = STRIDED ? 0 : blockIdx.x << LOG_E;
     auto gidx = [&](int li) -> int {
@@ -132,7 +185,10 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
         const int G = 8 >> nb;
         const int pos = FWD ? lo_bit + nbits - done - nb : lo_bit + done;   // lowest bit of this round
         const int ptop = pos + nb - 1;
-        u64 v[8]; int li[8]; int twb[8];
+        // which register pairs sit in adjacent words (-> 128-bit global accesses): with pos == 0 elements e, e+1;
+        // with pos > 0 and G >= 2 the same k of groups g, g+1 (bit 0 of the local index is bit 0 of g)
+        const int pair_step = pos == 0 ? 1 : (G >= 2 ? (1 << nb) : 0);
+        T v[8]; int li[8]; int twb[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             int g = e >> nb, k = e & ((1 << nb) - 1);
@@ -142,37 +198,68 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
         for (int g = 0; g < 8; ++g)
             twb[g] = (1 << (TOP - ptop)) + ((tid * G + g) >> pos) + (tile_base >> (ptop + 1));
         if (r == 0) {
+            u64 w[8];
+            if (pair_step) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = src[gidx(li[e])];
+                for (int e = 0; e < 8; ++e)
+                    if (!(e & pair_step)) {
+                        const ulonglong2 t = *(const ulonglong2*)(src + gidx(li[e]));
+                        w[e] = t.x; w[e + pair_step] = t.y;
+                    }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) w[e] = src[gidx(li[e])];
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = FINAL ? ar.from_raw(w[e]) : ar.from_word(w[e]);
         } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = sm[swz(li[e])];
+            for (int e = 0; e < 8; ++e) v[e] = ar.from_raw(sm[swz(li[e])]);
         }
         if (FWD) {
-            if (nb == 3) fwd_radix<3>(v, tw, twb, q); else if (nb == 2) fwd_radix<2>(v, tw, twb, q); else fwd_radix<1>(v, tw, twb, q);
+            if (nb == 3) fwd_radix<3>(ar, v, tw, twb); else if (nb == 2) fwd_radix<2>(ar, v, tw, twb); else fwd_radix<1>(ar, v, tw, twb);
+        } else if (FINAL && r == NR - 1) {
+            if (nb == 3) inv_radix<3, false>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, false>(ar, v, tw, twb); else inv_radix<1, false>(ar, v, tw, twb);
         } else {
-            if (nb == 3) inv_radix<3>(v, tw, twb, q); else if (nb == 2) inv_radix<2>(v, tw, twb, q); else inv_radix<1>(v, tw, twb, q);
+            if (nb == 3) inv_radix<3, true>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, true>(ar, v, tw, twb); else inv_radix<1, true>(ar, v, tw, twb);
         }
         done += nb;
         if (r == NR - 1) {
-            if (FINAL) {
-                if (FWD) {
+            u64 w[8];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) { u64 x = v[e]; x = x >= 2 * q ? x - 2 * q : x; v[e] = x >= q ? x - q : x; }
-                } else {
-                    const ulonglong2 ni = ninv_all[ld.mod];
+            for (int e = 0; e < 8; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
+            if (pair_step) {
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) v[e] = shoup_mul(v[e], ni.x, ni.y, q);
-                }
+                for (int e = 0; e < 8; ++e)
+                    if (!(e & pair_step)) *(ulonglong2*)(dst + gidx(li[e])) = make_ulonglong2(w[e], w[e + pair_step]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) dst[gidx(li[e])] = w[e];
             }
-#pragma unroll
-            for (int e = 0; e < 8; ++e) dst[gidx(li[e])] = v[e];
         } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) sm[swz(li[e])] = v[e];
+            for (int e = 0; e < 8; ++e) sm[swz(li[e])] = ar.to_raw(v[e]);
             __syncthreads();
         }
     }
+}
+
+template <int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
+__global__ void __launch_bounds__(1 << (LOG_E - 3))
+ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
+         const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all,
+         const ulonglong2* __restrict__ ninv_all, int logN) {
+    __shared__ __align__(16) u64 sm[1 << LOG_E];
+    const LimbDesc ld = limbs[blockIdx.y];
+    const size_t N = (size_t)1 << logN;
+    const ModConst& m = mc[ld.mod];
+    const u64* src = in + (size_t)ld.in_off * N;
+    u64* dst = out + (size_t)ld.out_off * N;
+    const ulonglong2 ni = ninv_all[ld.mod];
+    if (m.bits <= F64_MAX_BITS)
+        ntt_body<ArithF64, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithF64(m), sm, src, dst, twd_all + (size_t)ld.mod * N, ni, logN);
+    else
+        ntt_body<ArithInt, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithInt(m), sm, src, dst, tw_all + (size_t)ld.mod * N, ni, logN);
 }
 
 }  // namespace
@@ -204,9 +291,9 @@ void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
-    OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
+    OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
     OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, true, true>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
-              (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
+              (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
 }
 
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
@@ -214,8 +301,8 @@ void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
     OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, false, false>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
-              in, out, p.first, c.dmc(), c.tw_inv(), c.d_ninv.as<ulonglong2>(), c.logN);
-    OB_NTT_STRIDED_SWITCH(false, true, (const u64*)out, out, p.second, c.dmc(), c.tw_inv(), c.d_ninv.as<ulonglong2>(), c.logN)
+              in, out, p.first, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN);
+    OB_NTT_STRIDED_SWITCH(false, true, (const u64*)out, out, p.second, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN)
 }
 
 }  // namespace ob

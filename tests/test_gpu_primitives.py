@@ -9,6 +9,9 @@ CASES = [  # (logN, LogQ, LogP)
     (13, [29, 26, 26, 26, 26, 26], [29, 29]),          # configs/mlp.yml
     (14, [60, 30, 30, 30, 30, 30, 30], [60, 60]),      # configs/lola2.yml
     (13, [55, 40, 40, 40, 40, 40, 40], [61, 61, 61]),  # partial last digit (7 = 3+3+1)
+    (16, [60, 46, 45, 47, 46], [61, 46]),              # both sides of the FP64 / integer butterfly split (46 bits)
+    (15, [46, 46, 46, 46], [46, 46]),                  # FP64 butterflies only, largest admissible primes
+    (17, [45, 45], [45]),                              # deepest transform (17 stages) on the FP64 path
 ]
 
 
