@@ -70,6 +70,12 @@ void* B200_EvkToDevice(void* ctx, const uint64_t* evk_host);  /* free with B200_
 /* out [2][level+1][N] = KeySwitch(c1 [level+1][N]); addend_c0 (may be NULL) is added to polynomial 0 */
 void  B200_KeySwitch(void* ctx, int level, const uint64_t* c1, const void* evk_dev, const uint64_t* addend_c0, uint64_t* out);
 void  B200_KeySwitchDev(void* ctx, int level, const void* c1, const void* evk_dev, const void* addend_c0, void* out);
+/* n independent key switches on HOST buffers in one call, H2D / compute / D2H overlapped on three streams.
+ * ct_in[i]: [2][level+1][N] = (c0, c1) when has_c0 (out = KeySwitch(c1) + (c0, 0)), else [level+1][N] = c1.
+ * This is the host-buffer entry point a cgo/ctypes caller of lattigo/evaluator.go:61-81 (RotateNew on a batch of
+ * ciphertexts) would bind; out[i]: [2][level+1][N]. */
+void  B200_KeySwitchBatch(void* ctx, int level, int n, const uint64_t* const* ct_in, int has_c0, const void* const* evk_dev,
+                          uint64_t* const* out);
 void  B200_Decompose(void* ctx, int level, const uint64_t* c1, uint64_t* digits);   /* [beta][level+1+nP][N] */
 void  B200_ModDown(void* ctx, int level, const uint64_t* accQP, uint64_t* outQ);
 

@@ -127,7 +127,7 @@ struct Bootstrapper {
     scale_t built_for_scale = 0;
     u64 built_for_k = 0;
 };
-std::map<int, std::unique_ptr<Bootstrapper>> g_boot;     // keyed by slot count (LG/bootstrapper.go:16)
+std::map<int, std::unique_ptr<Bootstrapper>>& g_boot = *new std::map<int, std::unique_ptr<Bootstrapper>>();     // keyed by slot count (LG/bootstrapper.go:16)
 
 std::vector<double> cheb_interp(int deg, double K1, int r) {
     const int n = deg + 1;

@@ -14,7 +14,7 @@
 using namespace ob;
 
 namespace ob {
-std::unique_ptr<Scheme> g_scheme;
+std::unique_ptr<Scheme>& g_scheme = *new std::unique_ptr<Scheme>();   // heap-allocated and never destroyed: no static-destruction-order hazards (and no CUDA calls) at process exit
 static u64 g_seed = 0;
 static bool g_seed_set = false;
 Scheme& S() {

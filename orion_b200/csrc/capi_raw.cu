@@ -153,6 +153,62 @@ void B200_KeySwitch(void* h, int level, const uint64_t* c1, const void* evk_dev,
     d2h(out, dout.p, 2 * LN * 8);
 }
 
+// ---- batched key switch on HOST buffers, pipelined: upload of ciphertext i+1 (copy stream), key switch of i (compute
+//      stream) and download of i-1 (second copy stream) overlap, so the batch runs at max(H2D, compute, D2H) per
+//      ciphertext instead of their sum.  ct_in[i] is [2][L][N] (c0 then c1; out = KeySwitch(c1) + (c0, 0)) when
+//      has_c0 != 0, else [L][N] (c1 only).  Use pinned host memory (B200_HostAllocPinned) for true overlap. ----
+void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in, int has_c0, const void* const* evk_dev,
+                         uint64_t* const* out) {
+    RawCtx* r = R(h);
+    const size_t LN = (size_t)(level + 1) * r->ctx->N;
+    const size_t in_words = has_c0 ? 2 * LN : LN;
+    constexpr int NBUF = 3;
+    static cudaStream_t s_up = nullptr, s_down = nullptr;
+    static cudaEvent_t up_done[NBUF], comp_done[NBUF], down_done[NBUF];
+    static size_t slot_words = 0;
+    static void* d_in[NBUF]; static void* d_out[NBUF];
+    if (!s_up) {
+        OB_CUDA(cudaStreamCreateWithFlags(&s_up, cudaStreamNonBlocking));
+        OB_CUDA(cudaStreamCreateWithFlags(&s_down, cudaStreamNonBlocking));
+        for (int i = 0; i < NBUF; ++i) {
+            OB_CUDA(cudaEventCreateWithFlags(&up_done[i], cudaEventDisableTiming));
+            OB_CUDA(cudaEventCreateWithFlags(&comp_done[i], cudaEventDisableTiming));
+            OB_CUDA(cudaEventCreateWithFlags(&down_done[i], cudaEventDisableTiming));
+        }
+    }
+    if (slot_words < 2 * LN) {                              // (re)size the staging slots; plain cudaMalloc: used from 3 streams
+        OB_CUDA(cudaDeviceSynchronize());
+        for (int i = 0; i < NBUF; ++i) {
+            if (slot_words) { OB_CUDA(cudaFree(d_in[i])); OB_CUDA(cudaFree(d_out[i])); }
+            OB_CUDA(cudaMalloc(&d_in[i], 2 * LN * 8)); OB_CUDA(cudaMalloc(&d_out[i], 2 * LN * 8));
+        }
+        slot_words = 2 * LN;
+    }
+    cudaEvent_t start;                                      // the copy streams must not run ahead of work already queued
+    OB_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    OB_CUDA(cudaEventRecord(start, stream()));
+    OB_CUDA(cudaStreamWaitEvent(s_up, start, 0));
+    OB_CUDA(cudaStreamWaitEvent(s_down, start, 0));
+    for (int i = 0; i < n; ++i) {
+        const int sl = i % NBUF;
+        if (i >= NBUF) OB_CUDA(cudaStreamWaitEvent(s_up, comp_done[sl], 0));          // slot input free again
+        OB_CUDA(cudaMemcpyAsync(d_in[sl], ct_in[i], in_words * 8, cudaMemcpyHostToDevice, s_up));
+        OB_CUDA(cudaEventRecord(up_done[sl], s_up));
+        OB_CUDA(cudaStreamWaitEvent(stream(), up_done[sl], 0));
+        if (i >= NBUF) OB_CUDA(cudaStreamWaitEvent(stream(), down_done[sl], 0));      // slot output drained
+        const u64* c0 = has_c0 ? (const u64*)d_in[sl] : nullptr;
+        const u64* c1 = has_c0 ? (const u64*)d_in[sl] + LN : (const u64*)d_in[sl];
+        r->ev->keyswitch(level, c1, (const u64*)evk_dev[i], c0, level + 1, has_c0 ? 1 : 0, (u64*)d_out[sl], level + 1);
+        OB_CUDA(cudaEventRecord(comp_done[sl], stream()));
+        OB_CUDA(cudaStreamWaitEvent(s_down, comp_done[sl], 0));
+        OB_CUDA(cudaMemcpyAsync(out[i], d_out[sl], 2 * LN * 8, cudaMemcpyDeviceToHost, s_down));
+        OB_CUDA(cudaEventRecord(down_done[sl], s_down));
+    }
+    OB_CUDA(cudaStreamSynchronize(s_down));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    OB_CUDA(cudaEventDestroy(start));
+}
+
 // ---- pieces of the key switch, for stage-by-stage parity ----
 void B200_Decompose(void* h, int level, const uint64_t* c1, uint64_t* digits /* [beta][W][N], own limbs = c1 */) {
     RawCtx* r = R(h); Context& c = *r->ctx;

@@ -60,7 +60,7 @@ add_times_p_kernel(u64* __restrict__ acc, const u64* __restrict__ c, int N,
     acc[o] = add_mod(acc[o], shoup_mul(c[o], w.x, w.y, q), q);
 }
 
-HandleTable<LinearTransform> g_lts;
+HandleTable<LinearTransform>& g_lts = *new HandleTable<LinearTransform>();   // heap-allocated and never destroyed: no static-destruction-order hazards (and no CUDA calls) at process exit
 }  // namespace
 
 int lt_push(std::unique_ptr<LinearTransform> lt) { return g_lts.add(std::move(lt)); }

@@ -18,7 +18,7 @@
 namespace ob {
 
 namespace {
-HandleTable<Polynomial> g_polys;
+HandleTable<Polynomial>& g_polys = *new HandleTable<Polynomial>();   // heap-allocated and never destroyed: no static-destruction-order hazards (and no CUDA calls) at process exit
 
 int bitlen(int x) { int b = 0; while (x) { ++b; x >>= 1; } return b; }
 

@@ -205,7 +205,7 @@ void small_to_rns(Context& c, const int64_t* small, u64* out, const std::vector<
 
 // ---- FFT tables: roots of unity exp(2*pi*i*k/M), M = 2N, first quadrant from cos(), the rest by symmetry ----
 struct SchemeTables { FftTables fft; DevBuf pd; };
-static std::map<const Context*, std::unique_ptr<SchemeTables>> g_tables;
+static std::map<const Context*, std::unique_ptr<SchemeTables>>& g_tables = *new std::map<const Context*, std::unique_ptr<SchemeTables>>();   // heap-allocated and never destroyed: no static-destruction-order hazards (and no CUDA calls) at process exit
 
 void host_roots(int M, std::vector<double2>& r) {
     r.assign(M + 1, make_double2(0, 0));

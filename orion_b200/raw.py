@@ -42,6 +42,7 @@ RAW_SIGNATURES = {
     "B200_EvkToDevice": ([c_vp, u64p], c_vp),
     "B200_KeySwitch": ([c_vp, c_int, u64p, c_vp, u64p, u64p], None),
     "B200_KeySwitchDev": ([c_vp, c_int, c_vp, c_vp, c_vp, c_vp], None),
+    "B200_KeySwitchBatch": ([c_vp, c_int, c_int, ctypes.POINTER(c_vp), c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)], None),
     "B200_Decompose": ([c_vp, c_int, u64p, u64p], None),
     "B200_ModDown": ([c_vp, c_int, u64p, u64p], None),
     "B200_Rescale": ([c_vp, c_int, u64p, u64p, c_int], None),
@@ -150,6 +151,16 @@ class RawContext:
             c0p = _p(c0)
         self.lib.B200_KeySwitch(self.h, level, _p(c1), evk_dev, c0p, _p(out))
         return out
+
+    def keyswitch_batch(self, level, cts, evk_devs, has_c0=True):
+        """Pipelined batch on host arrays: cts[i] is [2][L][N] (c0, c1) if has_c0 else [L][N]; returns a list of [2][L][N]."""
+        n = len(cts)
+        cts = [np.ascontiguousarray(c, dtype=np.uint64) for c in cts]
+        outs = [np.empty((2, level + 1, self.N), dtype=np.uint64) for _ in range(n)]
+        arr = ctypes.c_void_p * n
+        self.lib.B200_KeySwitchBatch(self.h, level, n, arr(*[c.ctypes.data for c in cts]), 1 if has_c0 else 0,
+                                     arr(*evk_devs), arr(*[o.ctypes.data for o in outs]))
+        return outs
 
     def decompose(self, level, c1):
         c1 = np.ascontiguousarray(c1, dtype=np.uint64).reshape(level + 1, self.N)

@@ -114,4 +114,13 @@ def test_keyswitch_stages_and_full(orc, b200lib, case):
         ref2 = ref.copy()
         ref2[0] = oc.elementwise("add", ref[0], c0)
         assert np.array_equal(out2, ref2)
+    # batched, pipelined host-buffer entry point: same results as one call per ciphertext
+    level = oc.nQ - 1
+    cts = [np.stack([oc.uniform_poly(rng, list(range(level + 1))) for _ in range(2)]) for _ in range(5)]
+    outs = gc.keyswitch_batch(level, cts, [evk_dev] * 5)
+    for ct, o in zip(cts, outs):
+        assert np.array_equal(o, gc.keyswitch(level, ct[1], evk_dev, c0=ct[0]))
+    outs = gc.keyswitch_batch(level, [ct[1] for ct in cts], [evk_dev] * 5, has_c0=False)
+    for ct, o in zip(cts, outs):
+        assert np.array_equal(o, gc.keyswitch(level, ct[1], evk_dev))
     gc.lib.B200_DevFree(evk_dev)

@@ -1,0 +1,39 @@
+"""Driver for profiling the ResNet-20 trace replay: setup + warm-up inference + one timed inference."""
+import os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from orion_b200 import raw
+from orion_b200.bindings import B200Library
+from orion_b200.replay import Replayer, Trace
+lib = raw.load()
+gold = os.path.join(ROOT, "tests", "golden")
+B = B200Library(); B.B200_SetSeed(42)
+t = Trace(os.path.join(gold, "trace_resnet20.json"), os.path.join(gold, "trace_resnet20.npz"))
+r = Replayer(B, t, seed=1234)
+r.setup(); lib.B200_Sync()
+print("setup_launches", lib.B200_LaunchCount(), flush=True)
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+for i in range(n):
+    l0 = lib.B200_LaunchCount(); t0 = time.perf_counter()
+    r.infer(); lib.B200_Sync()
+    print("infer %d: %.3f s, %d launches" % (i, time.perf_counter() - t0, lib.B200_LaunchCount() - l0), flush=True)
+    if i == 0:
+        import collections
+        c = collections.Counter()
+        print("op counts", dict(r.counts))
+
+if "--by-op" in sys.argv:
+    import collections
+    tsum, lsum, cnt = collections.Counter(), collections.Counter(), collections.Counter()
+    orig = r._run
+    def timed(i, op):
+        lib.B200_Sync(); l0 = lib.B200_LaunchCount(); t0 = time.perf_counter()
+        orig(i, op)
+        lib.B200_Sync()
+        tsum[op[0]] += time.perf_counter() - t0; lsum[op[0]] += lib.B200_LaunchCount() - l0; cnt[op[0]] += 1
+    r._run = timed
+    r.infer()
+    tot = sum(tsum.values())
+    for k, v in tsum.most_common(14):
+        print("%-26s n=%4d  %8.1f ms  %5.1f%%  %7d launches  (%.1f us/launch)" % (k, cnt[k], v * 1e3, 100 * v / tot, lsum[k], 1e6 * v / max(1, lsum[k])))
+    print("total %.3f s" % tot)
