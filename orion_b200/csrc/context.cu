@@ -285,4 +285,13 @@ const uint32_t* Context::galois_index(u64 galEl) {
     return it->second->as<uint32_t>();
 }
 
+// the gather table of g^-1 is the scatter table of g (position of exponent e -> position of exponent g*e)
+const uint32_t* Context::galois_scatter(u64 galEl) {
+    const u64 mask = 2ull * N - 1;
+    u64 inv = 1, b = galEl & mask;
+    for (u64 e = (u64)N - 1; e; e >>= 1) { if (e & 1) inv = (inv * b) & mask; b = (b * b) & mask; }   // g^(phi(2N)-1), phi = N
+    OB_CHECK(((inv * galEl) & mask) == 1, "Galois element is not a unit mod 2N");
+    return galois_index(inv);
+}
+
 }  // namespace ob

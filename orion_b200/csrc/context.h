@@ -60,6 +60,7 @@ struct Context {
     const LimbDesc* limb_list(const std::vector<LimbDesc>& v);
     const BaseConv& base_conv(const std::vector<int>& src, const std::vector<int>& dst);
     const uint32_t* galois_index(u64 galEl);          // NTT-domain gather table, out[i] = in[idx[i]]
+    const uint32_t* galois_scatter(u64 galEl);        // inverse permutation: out[sc[i]] = in[i]
     u64 galois_element(int rot) const;                // 5^rot mod 2N
     u64 galois_conj() const { return 2ull * N - 1; }
 

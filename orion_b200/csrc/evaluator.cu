@@ -74,14 +74,77 @@ void PolyEvaluator::decompose(int level, const u64* c1_ntt, u64* digits) {
 
 void PolyEvaluator::moddown(int level, const u64* acc, int polys, const u64* addend, int addend_stride,
                             int addend_polys, u64* out, int out_stride) {
-    OB_CHECK(polys == 1 || polys == 2, "moddown handles 1 or 2 polynomials");
+    moddown_n(level, acc, ks_plan(level).W, polys, addend, addend_stride, addend_polys, out, out_stride);
+}
+
+void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, const u64* addend, int addend_stride,
+                              int addend_polys, u64* out, int out_stride) {
+    OB_CHECK(n >= 1 && n <= 4096, "moddown_n: polynomial count out of range");
     const KsPlan& p = ks_plan(level);
     const size_t N = ctx.N;
-    DevBuf pc((size_t)polys * p.K * N * 8), conv((size_t)polys * p.L * N * 8);
-    ntt_inverse(ctx, acc, pc.u(), p.intt_p[polys]);
-    base_convert_batch(ctx, p.moddown_b[polys], pc.u(), conv.u(), true);
-    ntt_forward(ctx, conv.u(), conv.u(), p.ntt_conv[polys]);
-    moddown_finish(ctx, level, acc, p.W, conv.u(), addend, addend_stride, addend_polys, out, out_stride, polys);
+    const int L = p.L, K = p.K;
+    const std::vector<int> key{level, n, acc_stride};
+    auto it = moddown_n_.find(key);
+    if (it == moddown_n_.end()) {
+        ModDownNPlan mp;
+        std::vector<LimbDesc> ip, nc;
+        std::vector<BaseConvPlan> pl(n, p.moddown);
+        std::vector<int> io, ob;
+        for (int z = 0; z < n; ++z) {
+            for (int k = 0; k < K; ++k)
+                ip.push_back(LimbDesc{(uint32_t)(z * acc_stride + L + k), (uint32_t)(z * K + k), (uint32_t)(ctx.nQ + k), 0});
+            for (int i = 0; i < L; ++i)
+                nc.push_back(LimbDesc{(uint32_t)(z * L + i), (uint32_t)(z * L + i), (uint32_t)i, 0});
+            io.push_back(z * K); ob.push_back(z * L);
+        }
+        mp.intt = make_ntt_plan(ctx, ip);
+        mp.bc = make_baseconv_batch(ctx, pl, io, ob);
+        mp.ntt = make_ntt_plan(ctx, nc);
+        it = moddown_n_.emplace(key, mp).first;
+    }
+    const ModDownNPlan& mp = it->second;
+    DevBuf pc((size_t)n * K * N * 8), conv((size_t)n * L * N * 8);
+    ntt_inverse(ctx, acc, pc.u(), mp.intt);
+    base_convert_batch(ctx, mp.bc, pc.u(), conv.u(), true);
+    ntt_forward(ctx, conv.u(), conv.u(), mp.ntt);
+    moddown_finish(ctx, level, acc, acc_stride, conv.u(), addend, addend_stride, addend_polys, out, out_stride, n);
+}
+
+void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits) {
+    OB_CHECK(n >= 1 && n <= 4096, "decompose_n: polynomial count out of range");
+    const KsPlan& p = ks_plan(level);
+    const int L = p.L, K = p.K, W = p.W, beta = p.beta;
+    const std::vector<int> key{level, n, c1_stride};
+    auto it = decomp_n_.find(key);
+    if (it == decomp_n_.end()) {
+        DecompNPlan dp;
+        std::vector<LimbDesc> il, dl;
+        std::vector<BaseConvPlan> pl;
+        std::vector<int> io, ob;
+        for (int z = 0; z < n; ++z) {
+            for (int i = 0; i < L; ++i)
+                il.push_back(LimbDesc{(uint32_t)(z * c1_stride + i), (uint32_t)(z * L + i), (uint32_t)i, 0});
+            for (int j = 0; j < beta; ++j) {
+                const int s0 = j * K, s1 = std::min((j + 1) * K, L);
+                for (int t = 0; t < W; ++t) {
+                    if (t >= s0 && t < s1) continue;
+                    const int ci = t < L ? t : ctx.nQ + (t - L);
+                    const uint32_t o = (uint32_t)((z * beta + j) * W + t);
+                    dl.push_back(LimbDesc{o, o, (uint32_t)ci, 0});
+                }
+                pl.push_back(p.modup[j]); io.push_back(z * L + s0); ob.push_back(z * beta * W);
+            }
+        }
+        dp.intt = make_ntt_plan(ctx, il);
+        dp.bc = make_baseconv_batch(ctx, pl, io, ob);
+        dp.ntt = make_ntt_plan(ctx, dl);
+        it = decomp_n_.emplace(key, dp).first;
+    }
+    const DecompNPlan& dp = it->second;
+    DevBuf coef((size_t)n * L * ctx.N * 8);
+    ntt_inverse(ctx, c1s, coef.u(), dp.intt);
+    base_convert_batch(ctx, dp.bc, coef.u(), digits, false);
+    ntt_forward(ctx, digits, digits, dp.ntt);
 }
 
 void PolyEvaluator::keyswitch(int level, const u64* c1_ntt, const u64* evk, const u64* addend, int addend_stride,

@@ -37,11 +37,22 @@ class PolyEvaluator {
     // in [polys][level+1][N] (stride in_stride) -> out [polys][level][N]
     void rescale(int level, const u64* in, int in_stride, u64* out, int out_stride, int polys);
 
+    // ---- batched variants: n independent polynomials in one set of launches (hoisted BSGS giant steps) ----
+    // c1s: polynomial z at c1s + z*c1_stride*N ([L][N]);  digits: [n][beta][W][N]
+    void decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits);
+    // acc: polynomial z at acc + z*acc_stride*N ([W][N] QP);  out: polynomial z at out + z*out_stride*N ([L][N])
+    void moddown_n(int level, const u64* acc, int acc_stride, int n, const u64* addend, int addend_stride, int addend_polys,
+                   u64* out, int out_stride);
+
     size_t digits_words(int level) const { return (size_t)ctx.num_digits(level) * (level + 1 + ctx.nP) * ctx.N; }
 
   private:
     std::map<int, std::unique_ptr<KsPlan>> plans_;
     std::map<int, NttPlan> rescale_intt_[3], rescale_ntt_[3];
+    struct DecompNPlan { NttPlan intt, ntt; BaseConvBatch bc; };
+    struct ModDownNPlan { NttPlan intt, ntt; BaseConvBatch bc; };
+    std::map<std::vector<int>, DecompNPlan> decomp_n_;
+    std::map<std::vector<int>, ModDownNPlan> moddown_n_;
 };
 
 }  // namespace ob

@@ -48,6 +48,18 @@ void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* 
 void ks_inner_product(Context& c, int level, const u64* c1_ntt, const u64* digits, const u64* evk,
                       u64* acc /* [2][W][N] */, const uint32_t* gather, bool accumulate);
 
+// n independent inner products in one launch (blockIdx.z): product z uses c1 + z*c1_zstride, digits + z*dig_zstride,
+// key m.evk[z]; adds the c0 contribution (add_mode 1: P * addend_z over the Q limbs, 2: addend_z over all W limbs, 0: none)
+// to polynomial 0 and writes through the scatter table m.scatter[z] (NTT-domain automorphism; nullptr = identity).
+constexpr int IPM_MAX = 48;
+struct IpMulti { const u64* evk[IPM_MAX]; const uint32_t* scatter[IPM_MAX]; };
+void ks_inner_product_multi(Context& c, int level, int n, const u64* c1, size_t c1_zstride, const u64* digits, size_t dig_zstride,
+                            const IpMulti& m, u64* out, size_t out_zstride, int add_mode, const u64* addend, size_t addend_zstride);
+// out[2][W][N] = sum of n QP ciphertexts
+constexpr int SUM_MAX = 64;
+struct SumList { const u64* p[SUM_MAX]; };
+void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out);
+
 // out[p][i][x] = (acc[p][i][x] - conv[p][i][x]) * P^-1 (+ addend[p][i][x])   i <= level; acc has stride W limbs
 void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
                     int addend_stride, int addend_polys, u64* out, int out_stride, int polys);

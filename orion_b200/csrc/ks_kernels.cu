@@ -147,6 +147,62 @@ inner_product_kernel(const u64* __restrict__ c1, const u64* __restrict__ digits,
     acc[o0] = r0; acc[o1] = r1;
 }
 
+// Batched inner product: blockIdx.z selects one of several independent (digits, evaluation key) pairs -- the baby steps
+// (shared digits, one key each) or the giant steps (own digits, one key each) of a hoisted BSGS linear transform.
+// Fused epilogue: the c0 contribution is added to polynomial 0 and the result is written through the NTT-domain
+// automorphism of that step (scatter table), replacing three extra launches per step.
+//   ADD_MODE 1: += (P mod q_t) * addend[z][t][x] for t < L   (baby steps: c0 lifted to QP)
+//   ADD_MODE 2: += addend[z][t][x] for every t                (giant steps: the c0 half of the inner sum, already in QP)
+template <int ADD_MODE>
+__global__ void __launch_bounds__(TPB)
+inner_product_multi_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restrict__ digits, size_t dig_zstride,
+                           const IpMulti m, u64* __restrict__ out, size_t out_zstride,
+                           const u64* __restrict__ addend, size_t addend_zstride,
+                           int N, int L, int K, int nQ, int nmod, int beta,
+                           const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, z = blockIdx.z, W = L + K;
+    const int x = blockIdx.x * TPB + threadIdx.x;
+    const int ci = t < L ? t : nQ + (t - L);
+    const ModConst mm = mc[ci];
+    const int own = t < L ? t / K : -1;
+    const u64* __restrict__ evk = m.evk[z];
+    const u64* __restrict__ c1z = c1 + (size_t)z * c1_zstride;
+    const u64* __restrict__ dz = digits + (size_t)z * dig_zstride;
+    u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
+    for (int j = 0; j < beta; ++j) {
+        const u64 d = (j == own) ? c1z[(size_t)t * N + x] : dz[((size_t)j * W + t) * N + x];
+        const u64 k0 = evk[(((size_t)j * 2 + 0) * nmod + ci) * N + x];
+        const u64 k1 = evk[(((size_t)j * 2 + 1) * nmod + ci) * N + x];
+        mac128(h0, l0, d, k0, mm.q);
+        mac128(h1, l1, d, k1, mm.q);
+    }
+    u64 r0 = mont_redc(h0, l0, mm.q, mm.qinv_neg), r1 = mont_redc(h1, l1, mm.q, mm.qinv_neg);
+    if (ADD_MODE == 1) {
+        if (t < L) { const ulonglong2 w = pmodq[t]; r0 = add_mod(r0, shoup_mul(addend[(size_t)z * addend_zstride + (size_t)t * N + x], w.x, w.y, mm.q), mm.q); }
+    } else if (ADD_MODE == 2) {
+        r0 = add_mod(r0, addend[(size_t)z * addend_zstride + (size_t)t * N + x], mm.q);
+    }
+    const uint32_t* __restrict__ sc = m.scatter[z];
+    const int xo = sc ? (int)__ldg(&sc[x]) : x;
+    u64* o = out + (size_t)z * out_zstride;
+    o[(size_t)t * N + xo] = r0; o[((size_t)W + t) * N + xo] = r1;
+}
+
+// out[p][t][x] = sum_z in[z][p][t][x]  (mod q_t), QP layout with W limbs per polynomial
+__global__ void __launch_bounds__(TPB)
+sum_qp_kernel(const SumList lst, int n, u64* __restrict__ out, int N, int L, int W, int nQ, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, p = blockIdx.z;
+    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
+    const u64 q = mc[t < L ? t : nQ + (t - L)].q;
+    const size_t o = ((size_t)p * W + t) * N + x;
+    ulonglong2 a = *(const ulonglong2*)(lst.p[0] + o);
+    for (int z = 1; z < n; ++z) {
+        const ulonglong2 b = *(const ulonglong2*)(lst.p[z] + o);
+        a.x = add_mod(a.x, b.x, q); a.y = add_mod(a.y, b.y, q);
+    }
+    *(ulonglong2*)(out + o) = a;
+}
+
 __global__ void __launch_bounds__(TPB)
 moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __restrict__ conv, int L,
                       const u64* __restrict__ addend, int addend_stride, int addend_polys,
@@ -265,6 +321,24 @@ void ks_inner_product(Context& c, int level, const u64* c1_ntt, const u64* digit
     if (gather) { if (accumulate) OB_IP(true, true); else OB_IP(true, false); }
     else        { if (accumulate) OB_IP(false, true); else OB_IP(false, false); }
 #undef OB_IP
+}
+
+void ks_inner_product_multi(Context& c, int level, int n, const u64* c1, size_t c1_zstride, const u64* digits, size_t dig_zstride,
+                            const IpMulti& m, u64* out, size_t out_zstride, int add_mode, const u64* addend, size_t addend_zstride) {
+    OB_CHECK(n >= 1 && n <= IPM_MAX, "inner product batch size");
+    const int L = level + 1, K = c.nP, W = L + K, beta = c.num_digits(level);
+    dim3 grid(c.N / TPB, W, n);
+#define OB_IPM(MODE) OB_LAUNCH((inner_product_multi_kernel<MODE>), grid, TPB, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out, \
+                               out_zstride, addend, addend_zstride, c.N, L, K, c.nQ, c.nmod, beta, c.d_pmodq.as<ulonglong2>(), c.dmc())
+    if (add_mode == 1) OB_IPM(1); else if (add_mode == 2) OB_IPM(2); else OB_IPM(0);
+#undef OB_IPM
+}
+
+void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out) {
+    OB_CHECK(n >= 1 && n <= SUM_MAX, "sum_qp count");
+    const int L = level + 1, W = L + c.nP;
+    dim3 grid(c.N / (2 * TPB), W, 2);
+    OB_LAUNCH(sum_qp_kernel, grid, TPB, 0, stream(), lst, n, out, c.N, L, W, c.nQ, c.dmc());
 }
 
 void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,

@@ -21,14 +21,20 @@ namespace ob {
 namespace {
 constexpr int TPB = 256;
 
-// acc[c][t][x] = REDC( sum_k diag[pairs[k].x][td][x] * rot[pairs[k].y][c][t][x] ),  td = diag limb of t
+// acc[z][c][t][x] = REDC( sum_k diag[pairs_z[k].x][td][x] * rot[pairs_z[k].y][c][t][x] ),  td = diag limb of t;
+// blockIdx.z = giant step z (all giant steps of a transform in one launch)
+constexpr int LTM_MAX = 64;
+struct LtMacMulti { const int2* pairs[LTM_MAX]; int np[LTM_MAX]; };
 __global__ void __launch_bounds__(TPB)
-lt_mac_kernel(const u64* __restrict__ diags, const u64* __restrict__ rots, const int2* __restrict__ pairs, int npairs,
-              u64* __restrict__ acc, int N, int L, int W, int L_lt, int W_lt, int nQ, const ModConst* __restrict__ mc) {
-    const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
+lt_mac_kernel(const u64* __restrict__ diags, const u64* __restrict__ rots, const LtMacMulti mm, u64* __restrict__ acc_all,
+              int N, int L, int W, int L_lt, int W_lt, int nQ, const ModConst* __restrict__ mc) {
+    const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x, z = blockIdx.z;
     const int ci = t < L ? t : nQ + (t - L);
     const int td = t < L ? t : L_lt + (t - L);
     const ModConst m = mc[ci];
+    const int2* __restrict__ pairs = mm.pairs[z];
+    const int npairs = mm.np[z];
+    u64* acc = acc_all + (size_t)z * 2 * W * N;
     u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
     for (int k = 0; k < npairs; ++k) {
         const int2 pr = __ldg(&pairs[k]);
@@ -167,48 +173,70 @@ std::unique_ptr<Ciphertext> lt_apply(Scheme& s, const LinearTransform& lt, const
     ew_binary(c, EW_COPY, in.data.u(), in_stride, nullptr, 0, 1, ct.u(), L, 2, L, L);
     const u64* c0 = ct.u(); const u64* c1 = ct.u() + (size_t)L * N;
 
-    DevBuf digits(s.pev->digits_words(level) * 8), rots((size_t)nb * PW * 8), tmp(PW * 8);
-    bool need_digits = false;
-    for (int i : lt.babies) if (i) need_digits = true;
-    if (need_digits) s.pev->decompose(level, c1, digits.u());
-    for (int k = 0; k < nb; ++k) {
-        const int i = lt.babies[k];
-        u64* r = rots.u() + (size_t)k * PW;
-        if (i == 0) {
-            OB_LAUNCH(lift_times_p_kernel, dim3(N / TPB, W, 2), TPB, 0, stream(), ct.u(), L, r, N, L, W, pmodq, c.dmc());
-            continue;
+    // ---- baby steps: one decomposition (hoisting), then ALL rotations in one launch: inner product with evk_i,
+    //      + P*c0, written through the automorphism's scatter table ----
+    const size_t dig_words = s.pev->digits_words(level);
+    DevBuf digits(dig_words * 8), rots((size_t)nb * PW * 8);
+    int k_first = 0;
+    if (nb > 0 && lt.babies[0] == 0) {
+        OB_LAUNCH(lift_times_p_kernel, dim3(N / TPB, W, 2), TPB, 0, stream(), ct.u(), L, rots.u(), N, L, W, pmodq, c.dmc());
+        k_first = 1;
+    }
+    if (nb > k_first) {
+        s.pev->decompose(level, c1, digits.u());
+        for (int k0 = k_first; k0 < nb; k0 += IPM_MAX) {
+            const int n = std::min(IPM_MAX, nb - k0);
+            IpMulti m{};
+            for (int k = 0; k < n; ++k) {
+                const u64 g = c.galois_element(lt.babies[k0 + k]);
+                m.evk[k] = s.galois_key(g).data.u(); m.scatter[k] = c.galois_scatter(g);
+            }
+            ks_inner_product_multi(c, level, n, c1, 0, digits.u(), 0, m, rots.u() + (size_t)k0 * PW, PW, 1, c0, 0);
         }
-        const u64 g = c.galois_element(i);
-        ks_inner_product(c, level, c1, digits.u(), s.galois_key(g).data.u(), tmp.u(), nullptr, false);
-        OB_LAUNCH(add_times_p_kernel, dim3(N / TPB, L), TPB, 0, stream(), tmp.u(), c0, N, pmodq, c.dmc());
-        automorphism_ntt(c, tmp.u(), r, 2 * W, c.galois_index(g));
     }
 
-    DevBuf out(PW * 8), acc(PW * 8), u1((size_t)L * N * 8), dig2(s.pev->digits_words(level) * 8), ks(PW * 8), rot(PW * 8);
-    bool first = true;
-    for (auto& kv : lt.index) {
-        const int j = kv.first, np = (int)kv.second.size();
-        u64* dst = (j == 0 && first) ? out.u() : acc.u();
-        OB_LAUNCH(lt_mac_kernel, dim3(N / TPB, W), TPB, 0, stream(), lt.diags.u(), rots.u(), lt.pairs.at(j).as<int2>(), np,
-                  dst, N, L, W, lt.level + 1, lt.W, c.nQ, c.dmc());
-        const u64* contrib = dst;
-        if (j != 0) {
-            const u64 g = c.galois_element(j);
-            s.pev->moddown(level, acc.u() + (size_t)W * N, 1, nullptr, 0, 0, u1.u(), L);
-            s.pev->decompose(level, u1.u(), dig2.u());
-            ks_inner_product(c, level, u1.u(), dig2.u(), s.galois_key(g).data.u(), ks.u(), nullptr, false);
-            // c0 half of the inner sum is added before the automorphism (it is already scaled by P)
-            ew_binary(c, EW_ADD, ks.u(), W, acc.u(), W, 1, ks.u(), W, 1, W, L);
-            automorphism_ntt(c, ks.u(), rot.u(), 2 * W, c.galois_index(g));
-            contrib = rot.u();
+    // ---- giant steps, batched: all inner sums in one launch; then for the rotated ones ModDown(c1 half) -> decompose ->
+    //      inner product with evk_j (+ c0 half, through the automorphism) as one launch sequence over all of them ----
+    std::vector<int> gj; std::vector<const DevBuf*> gp; std::vector<int> gn;
+    for (auto& kv : lt.index) { gj.push_back(kv.first); gp.push_back(&lt.pairs.at(kv.first)); gn.push_back((int)kv.second.size()); }
+    const int ng = (int)gj.size();
+    OB_CHECK(ng >= 1, "linear transform without diagonals");
+    const int z_first = gj[0] == 0 ? 1 : 0;                    // giant step 0 needs no rotation (std::map: it comes first)
+    // chunk so that the per-chunk digit buffers stay below ~6 GB
+    const int chunk = std::max(1, (int)std::min<size_t>(std::min(IPM_MAX, LTM_MAX), ((size_t)6 << 30) / (dig_words * 8 + 3 * PW * 8)));
+    DevBuf out(PW * 8);
+    bool have_out = false;
+    for (int zc = 0; zc < ng; zc += chunk) {
+        const int n = std::min(chunk, ng - zc);
+        DevBuf accs((size_t)n * PW * 8);
+        LtMacMulti mm{};
+        for (int z = 0; z < n; ++z) { mm.pairs[z] = gp[zc + z]->as<int2>(); mm.np[z] = gn[zc + z]; }
+        OB_LAUNCH(lt_mac_kernel, dim3(N / TPB, W, n), TPB, 0, stream(), lt.diags.u(), rots.u(), mm, accs.u(), N, L, W,
+                  lt.level + 1, lt.W, c.nQ, c.dmc());
+        const int zr = (zc == 0) ? z_first : 0;                 // first rotated step of this chunk
+        const int nr = n - zr;
+        SumList lst{}; int ns = 0;
+        if (have_out) lst.p[ns++] = out.u();
+        if (zr == 1) lst.p[ns++] = accs.u();
+        DevBuf rot_out((size_t)std::max(nr, 1) * PW * 8);
+        if (nr > 0) {
+            DevBuf u1((size_t)nr * L * N * 8), dig2((size_t)nr * dig_words * 8);
+            const u64* acc_r = accs.u() + (size_t)zr * PW;
+            s.pev->moddown_n(level, acc_r + (size_t)W * N, 2 * W, nr, nullptr, 0, 0, u1.u(), L);
+            s.pev->decompose_n(level, u1.u(), L, nr, dig2.u());
+            IpMulti m{};
+            for (int z = 0; z < nr; ++z) {
+                const u64 g = c.galois_element(gj[zc + zr + z]);
+                m.evk[z] = s.galois_key(g).data.u(); m.scatter[z] = c.galois_scatter(g);
+                lst.p[ns++] = rot_out.u() + (size_t)z * PW;
+            }
+            ks_inner_product_multi(c, level, nr, u1.u(), (size_t)L * N, dig2.u(), dig_words, m, rot_out.u(), PW, 2, acc_r, PW);
         }
-        if (first) {
-            if (contrib != out.u())
-                OB_CUDA(cudaMemcpyAsync(out.p, contrib, PW * 8, cudaMemcpyDeviceToDevice, stream()));
-            first = false;
-        } else {
-            ew_binary(c, EW_ADD, out.u(), W, contrib, W, 2, out.u(), W, 2, W, L);
-        }
+        if (ns == 1 && lst.p[0] != out.u())
+            OB_CUDA(cudaMemcpyAsync(out.p, lst.p[0], PW * 8, cudaMemcpyDeviceToDevice, stream()));
+        else if (ns > 1)
+            sum_qp(c, level, lst, ns, out.u());
+        have_out = true;
     }
     auto res = s.new_ct(level, 1, in.scale * lt.scale, in.log_slots);
     s.pev->moddown(level, out.u(), 2, nullptr, 0, 0, res->data.u(), L);
