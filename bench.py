@@ -9,6 +9,7 @@ Ciphertexts are sharded across ranks (no data-path collective): weak scaling.
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 """
 import argparse
+import ctypes
 import json
 import os
 import statistics
@@ -164,16 +165,18 @@ def main():
     host_out = [np.ctypeslib.as_array(ctypes_cast(lib.B200_HostAllocPinned(2 * LN), 2 * LN)) for _ in range(BATCH)]
     for b in range(BATCH):
         host_in[b][:] = rng.integers(0, 1 << 44, size=2 * LN, dtype=np.uint64)
-    dev_in = [lib.B200_DevAlloc(2 * LN) for _ in range(BATCH)]
-    dev_out = [lib.B200_DevAlloc(2 * LN) for _ in range(BATCH)]
+    dev_in = lib.B200_DevAlloc(BATCH * 2 * LN)          # [BATCH][2][L][N] = (c0, c1) per ciphertext
+    dev_out = lib.B200_DevAlloc(BATCH * 2 * LN)
     for b in range(BATCH):
-        lib.B200_Upload(dev_in[b], raw._p(host_in[b]), 2 * LN)
+        lib.B200_Upload(dev_in + b * 2 * LN * 8, raw._p(host_in[b]), 2 * LN)
+
+    GROUP = 8                                           # ciphertexts per launch sequence (digit buffers: 100 MB each)
 
     def step_resident(s):
-        for b in range(BATCH):
-            lib.B200_KeySwitchDev(ctx.h, level, dev_in[b] + LN * 8, evks[(s * BATCH + b) % N_EVK], dev_in[b], dev_out[b])
+        for b0 in range(0, BATCH, GROUP):
+            ek = (ctypes.c_void_p * GROUP)(*[evks[(s * BATCH + b0 + b) % N_EVK] for b in range(GROUP)])
+            lib.B200_KeySwitchBatchDev(ctx.h, level, GROUP, dev_in + b0 * 2 * LN * 8, 1, ek, dev_out + b0 * 2 * LN * 8)
 
-    import ctypes
     vp_arr = ctypes.c_void_p * BATCH
     in_ptrs = vp_arr(*[h.ctypes.data for h in host_in])
     out_ptrs = vp_arr(*[h.ctypes.data for h in host_out])
@@ -250,7 +253,7 @@ def main():
     # reference and replayed through the drop-in boundary; every rank runs its own image (image-sharded, no collective).
     resnet = None
     if not args.no_resnet:
-        for d in dev_in + dev_out + big + evks:
+        for d in [dev_in, dev_out] + big + evks:
             lib.B200_DevFree(d)
         ctx.close()
         resnet = run_resnet(lib, rank, world, dist if world > 1 else None, torch)

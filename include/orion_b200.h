@@ -76,6 +76,9 @@ void  B200_KeySwitchDev(void* ctx, int level, const void* c1, const void* evk_de
  * ciphertexts) would bind; out[i]: [2][level+1][N]. */
 void  B200_KeySwitchBatch(void* ctx, int level, int n, const uint64_t* const* ct_in, int has_c0, const void* const* evk_dev,
                           uint64_t* const* out);
+/* The same batch on device buffers: cts [n][2][level+1][N] (or [n][level+1][N] without c0), out [n][2][level+1][N];
+ * every kernel of the key switch is launched once for the whole batch. */
+void  B200_KeySwitchBatchDev(void* ctx, int level, int n, const void* cts, int has_c0, const void* const* evk_dev, void* out);
 void  B200_Decompose(void* ctx, int level, const uint64_t* c1, uint64_t* digits);   /* [beta][level+1+nP][N] */
 void  B200_ModDown(void* ctx, int level, const uint64_t* accQP, uint64_t* outQ);
 

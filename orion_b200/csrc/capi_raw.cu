@@ -153,16 +153,29 @@ void B200_KeySwitch(void* h, int level, const uint64_t* c1, const void* evk_dev,
     d2h(out, dout.p, 2 * LN * 8);
 }
 
-// ---- batched key switch on HOST buffers, pipelined: upload of ciphertext i+1 (copy stream), key switch of i (compute
-//      stream) and download of i-1 (second copy stream) overlap, so the batch runs at max(H2D, compute, D2H) per
+// ---- n independent key switches on device buffers, one launch sequence for the whole batch (every kernel covers all
+//      ciphertexts, so the short ModDown / rescale-sized launches fill the GPU).  cts: [n][2][L][N] = (c0, c1) when
+//      has_c0 (out = KeySwitch(c1) + (c0, 0)), else [n][L][N]; out: [n][2][L][N]. ----
+void B200_KeySwitchBatchDev(void* h, int level, int n, const void* cts, int has_c0, const void* const* evk_dev, void* out) {
+    RawCtx* r = R(h);
+    const int L = level + 1;
+    const size_t LN = (size_t)L * r->ctx->N;
+    const u64* base = (const u64*)cts;
+    r->ev->keyswitch_n(level, n, has_c0 ? base + LN : base, has_c0 ? 2 * L : L, (const u64* const*)evk_dev,
+                       has_c0 ? base : nullptr, 2 * L, (u64*)out);
+}
+
+// ---- batched key switch on HOST buffers, pipelined: upload of group g+1 (copy stream), key switch of group g (compute
+//      stream) and download of group g-1 (second copy stream) overlap, so the batch runs at max(H2D, compute, D2H) per
 //      ciphertext instead of their sum.  ct_in[i] is [2][L][N] (c0 then c1; out = KeySwitch(c1) + (c0, 0)) when
 //      has_c0 != 0, else [L][N] (c1 only).  Use pinned host memory (B200_HostAllocPinned) for true overlap. ----
 void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in, int has_c0, const void* const* evk_dev,
                          uint64_t* const* out) {
     RawCtx* r = R(h);
-    const size_t LN = (size_t)(level + 1) * r->ctx->N;
+    const int L = level + 1;
+    const size_t LN = (size_t)L * r->ctx->N;
     const size_t in_words = has_c0 ? 2 * LN : LN;
-    constexpr int NBUF = 3;
+    constexpr int NBUF = 3, GROUP = 4;                      // ciphertexts per pipeline stage
     static cudaStream_t s_up = nullptr, s_down = nullptr;
     static cudaEvent_t up_done[NBUF], comp_done[NBUF], down_done[NBUF];
     static size_t slot_words = 0;
@@ -176,32 +189,33 @@ void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in
             OB_CUDA(cudaEventCreateWithFlags(&down_done[i], cudaEventDisableTiming));
         }
     }
-    if (slot_words < 2 * LN) {                              // (re)size the staging slots; plain cudaMalloc: used from 3 streams
+    if (slot_words < GROUP * 2 * LN) {                      // (re)size the staging slots; plain cudaMalloc: used from 3 streams
         OB_CUDA(cudaDeviceSynchronize());
         for (int i = 0; i < NBUF; ++i) {
             if (slot_words) { OB_CUDA(cudaFree(d_in[i])); OB_CUDA(cudaFree(d_out[i])); }
-            OB_CUDA(cudaMalloc(&d_in[i], 2 * LN * 8)); OB_CUDA(cudaMalloc(&d_out[i], 2 * LN * 8));
+            OB_CUDA(cudaMalloc(&d_in[i], GROUP * 2 * LN * 8)); OB_CUDA(cudaMalloc(&d_out[i], GROUP * 2 * LN * 8));
         }
-        slot_words = 2 * LN;
+        slot_words = GROUP * 2 * LN;
     }
     cudaEvent_t start;                                      // the copy streams must not run ahead of work already queued
     OB_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
     OB_CUDA(cudaEventRecord(start, stream()));
     OB_CUDA(cudaStreamWaitEvent(s_up, start, 0));
     OB_CUDA(cudaStreamWaitEvent(s_down, start, 0));
-    for (int i = 0; i < n; ++i) {
-        const int sl = i % NBUF;
-        if (i >= NBUF) OB_CUDA(cudaStreamWaitEvent(s_up, comp_done[sl], 0));          // slot input free again
-        OB_CUDA(cudaMemcpyAsync(d_in[sl], ct_in[i], in_words * 8, cudaMemcpyHostToDevice, s_up));
+    int g = 0;
+    for (int i0 = 0; i0 < n; i0 += GROUP, ++g) {
+        const int m = std::min(GROUP, n - i0), sl = g % NBUF;
+        if (g >= NBUF) OB_CUDA(cudaStreamWaitEvent(s_up, comp_done[sl], 0));          // slot input free again
+        for (int z = 0; z < m; ++z)
+            OB_CUDA(cudaMemcpyAsync((u64*)d_in[sl] + (size_t)z * in_words, ct_in[i0 + z], in_words * 8, cudaMemcpyHostToDevice, s_up));
         OB_CUDA(cudaEventRecord(up_done[sl], s_up));
         OB_CUDA(cudaStreamWaitEvent(stream(), up_done[sl], 0));
-        if (i >= NBUF) OB_CUDA(cudaStreamWaitEvent(stream(), down_done[sl], 0));      // slot output drained
-        const u64* c0 = has_c0 ? (const u64*)d_in[sl] : nullptr;
-        const u64* c1 = has_c0 ? (const u64*)d_in[sl] + LN : (const u64*)d_in[sl];
-        r->ev->keyswitch(level, c1, (const u64*)evk_dev[i], c0, level + 1, has_c0 ? 1 : 0, (u64*)d_out[sl], level + 1);
+        if (g >= NBUF) OB_CUDA(cudaStreamWaitEvent(stream(), down_done[sl], 0));      // slot output drained
+        B200_KeySwitchBatchDev(h, level, m, d_in[sl], has_c0, evk_dev + i0, d_out[sl]);
         OB_CUDA(cudaEventRecord(comp_done[sl], stream()));
         OB_CUDA(cudaStreamWaitEvent(s_down, comp_done[sl], 0));
-        OB_CUDA(cudaMemcpyAsync(out[i], d_out[sl], 2 * LN * 8, cudaMemcpyDeviceToHost, s_down));
+        for (int z = 0; z < m; ++z)
+            OB_CUDA(cudaMemcpyAsync(out[i0 + z], (u64*)d_out[sl] + (size_t)z * 2 * LN, 2 * LN * 8, cudaMemcpyDeviceToHost, s_down));
         OB_CUDA(cudaEventRecord(down_done[sl], s_down));
     }
     OB_CUDA(cudaStreamSynchronize(s_down));

@@ -78,7 +78,7 @@ void PolyEvaluator::moddown(int level, const u64* acc, int polys, const u64* add
 }
 
 void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, const u64* addend, int addend_stride,
-                              int addend_polys, u64* out, int out_stride) {
+                              int addend_polys, u64* out, int out_stride, int addend_period, int addend_zstride) {
     OB_CHECK(n >= 1 && n <= 4096, "moddown_n: polynomial count out of range");
     const KsPlan& p = ks_plan(level);
     const size_t N = ctx.N;
@@ -107,7 +107,8 @@ void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, 
     ntt_inverse(ctx, acc, pc.u(), mp.intt);
     base_convert_batch(ctx, mp.bc, pc.u(), conv.u(), true);
     ntt_forward(ctx, conv.u(), conv.u(), mp.ntt);
-    moddown_finish(ctx, level, acc, acc_stride, conv.u(), addend, addend_stride, addend_polys, out, out_stride, n);
+    moddown_finish(ctx, level, acc, acc_stride, conv.u(), addend, addend_stride, addend_polys, out, out_stride, n,
+                   addend_period, addend_zstride);
 }
 
 void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits) {
@@ -154,6 +155,23 @@ void PolyEvaluator::keyswitch(int level, const u64* c1_ntt, const u64* evk, cons
     decompose(level, c1_ntt, digits.u());
     ks_inner_product(ctx, level, c1_ntt, digits.u(), evk, acc.u(), nullptr, false);
     moddown(level, acc.u(), 2, addend, addend_stride, addend_polys, out, out_stride);
+}
+
+void PolyEvaluator::keyswitch_n(int level, int n, const u64* c1s, int c1_zstride, const u64* const* evks, const u64* addend,
+                                int addend_zstride, u64* out) {
+    const KsPlan& p = ks_plan(level);
+    const size_t N = ctx.N, dw = digits_words(level);
+    for (int z0 = 0; z0 < n; z0 += IPM_MAX) {
+        const int m = std::min(IPM_MAX, n - z0);
+        DevBuf digits((size_t)m * dw * 8), acc((size_t)m * 2 * p.W * N * 8);
+        const u64* c1 = c1s + (size_t)z0 * c1_zstride * N;
+        decompose_n(level, c1, c1_zstride, m, digits.u());
+        IpMulti im{};
+        for (int z = 0; z < m; ++z) { im.evk[z] = evks[z0 + z]; im.scatter[z] = nullptr; }
+        ks_inner_product_multi(ctx, level, m, c1, (size_t)c1_zstride * N, digits.u(), dw, im, acc.u(), (size_t)2 * p.W * N, 0, nullptr, 0);
+        moddown_n(level, acc.u(), p.W, 2 * m, addend ? addend + (size_t)z0 * addend_zstride * N : nullptr, 0, addend ? 1 : 0,
+                  out + (size_t)z0 * 2 * p.L * N, p.L, 2, addend_zstride);
+    }
 }
 
 void PolyEvaluator::rescale(int level, const u64* in, int in_stride, u64* out, int out_stride, int polys) {

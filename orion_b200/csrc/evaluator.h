@@ -42,7 +42,11 @@ class PolyEvaluator {
     void decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits);
     // acc: polynomial z at acc + z*acc_stride*N ([W][N] QP);  out: polynomial z at out + z*out_stride*N ([L][N])
     void moddown_n(int level, const u64* acc, int acc_stride, int n, const u64* addend, int addend_stride, int addend_polys,
-                   u64* out, int out_stride);
+                   u64* out, int out_stride, int addend_period = 0, int addend_zstride = 0);
+    // n independent key switches in one launch sequence: c1 of ciphertext z at c1s + z*c1_zstride*N, key evks[z],
+    // optional addend (c0) at addend + z*addend_zstride*N; out: [n][2][L][N] contiguous
+    void keyswitch_n(int level, int n, const u64* c1s, int c1_zstride, const u64* const* evks, const u64* addend,
+                     int addend_zstride, u64* out);
 
     size_t digits_words(int level) const { return (size_t)ctx.num_digits(level) * (level + 1 + ctx.nP) * ctx.N; }
 

@@ -62,7 +62,8 @@ void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out);
 
 // out[p][i][x] = (acc[p][i][x] - conv[p][i][x]) * P^-1 (+ addend[p][i][x])   i <= level; acc has stride W limbs
 void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
-                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys);
+                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys,
+                    int addend_period = 0, int addend_zstride = 0);   // period > 0: polynomial z*period + c gets addend (z, c), c < addend_polys
 
 // rescale helpers (level -> level-1): see evaluator.cu
 void rescale_prep(Context& c, int level, const u64* last_coeff /* [polys][N] */, u64* tmp /* [polys][level][N] */, int polys);

@@ -205,7 +205,7 @@ sum_qp_kernel(const SumList lst, int n, u64* __restrict__ out, int N, int L, int
 
 __global__ void __launch_bounds__(TPB)
 moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __restrict__ conv, int L,
-                      const u64* __restrict__ addend, int addend_stride, int addend_polys,
+                      const u64* __restrict__ addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
                       u64* __restrict__ out, int out_stride, int N,
                       const ulonglong2* __restrict__ pinv, const ModConst* __restrict__ mc) {
     const int i = blockIdx.y, p = blockIdx.z;
@@ -217,8 +217,10 @@ moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __
     ulonglong2 r;
     r.x = shoup_mul(sub_mod(a.x, b.x, q), w.x, w.y, q);
     r.y = shoup_mul(sub_mod(a.y, b.y, q), w.x, w.y, q);
-    if (addend != nullptr && p < addend_polys) {
-        const ulonglong2 e = *(const ulonglong2*)(addend + ((size_t)p * addend_stride + i) * N + x);
+    // polynomial p = z*period + c receives addend polynomial c of group z when c < addend_polys
+    const int pz = p / addend_period, pc = p - pz * addend_period;
+    if (addend != nullptr && pc < addend_polys) {
+        const ulonglong2 e = *(const ulonglong2*)(addend + ((size_t)pz * addend_zstride + (size_t)pc * addend_stride + i) * N + x);
         r.x = add_mod(r.x, e.x, q); r.y = add_mod(r.y, e.y, q);
     }
     *(ulonglong2*)(out + ((size_t)p * out_stride + i) * N + x) = r;
@@ -342,10 +344,11 @@ void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out) {
 }
 
 void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
-                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys) {
+                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys, int addend_period, int addend_zstride) {
     dim3 grid(c.N / (2 * TPB), level + 1, polys);
+    if (addend_period <= 0) { addend_period = 1 << 30; addend_zstride = 0; }
     OB_LAUNCH(moddown_finish_kernel, grid, TPB, 0, stream(), acc, acc_stride, conv, level + 1, addend, addend_stride,
-              addend_polys, out, out_stride, c.N, c.d_pinv.as<ulonglong2>(), c.dmc());
+              addend_polys, addend_period, addend_zstride, out, out_stride, c.N, c.d_pinv.as<ulonglong2>(), c.dmc());
 }
 
 void rescale_prep(Context& c, int level, const u64* last_coeff, u64* tmp, int polys) {

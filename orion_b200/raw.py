@@ -43,6 +43,7 @@ RAW_SIGNATURES = {
     "B200_KeySwitch": ([c_vp, c_int, u64p, c_vp, u64p, u64p], None),
     "B200_KeySwitchDev": ([c_vp, c_int, c_vp, c_vp, c_vp, c_vp], None),
     "B200_KeySwitchBatch": ([c_vp, c_int, c_int, ctypes.POINTER(c_vp), c_int, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)], None),
+    "B200_KeySwitchBatchDev": ([c_vp, c_int, c_int, c_vp, c_int, ctypes.POINTER(c_vp), c_vp], None),
     "B200_Decompose": ([c_vp, c_int, u64p, u64p], None),
     "B200_ModDown": ([c_vp, c_int, u64p, u64p], None),
     "B200_Rescale": ([c_vp, c_int, u64p, u64p, c_int], None),
