@@ -239,6 +239,9 @@ const BaseConv& Context::base_conv(const std::vector<int>& src, const std::vecto
     int ns = (int)src.size(), nd = (int)dst.size();
     bc->ns = ns; bc->nd = nd; bc->h_src = src; bc->h_dst = dst;
     std::vector<u64> inv(2 * ns), mat((size_t)ns * nd), negvq((size_t)nd * (ns + 1)), hs(ns), hd(nd);
+    std::vector<double> matd((size_t)ns * nd), negd((size_t)nd * (ns + 1));
+    bc->f64_src = true;
+    for (int i = 0; i < ns; ++i) if (mc[src[i]].bits > 46) bc->f64_src = false;
     for (int i = 0; i < ns; ++i) {
         u64 qi = mod[src[i]], prod = 1;
         for (int k = 0; k < ns; ++k) if (k != i) prod = mulmod_u64(prod, mod[src[k]] % qi, qi);
@@ -251,14 +254,19 @@ const BaseConv& Context::base_conv(const std::vector<int>& src, const std::vecto
             u64 prod = 1;
             for (int k = 0; k < ns; ++k) if (k != i) prod = mulmod_u64(prod, mod[src[k]] % p, p);
             mat[(size_t)i * nd + d] = mulmod_u64(prod, mc[dst[d]].r1, p);
+            matd[(size_t)i * nd + d] = (double)prod;
             all = mulmod_u64(all, mod[src[i]] % p, p);
         }
-        for (int v = 0; v <= ns; ++v) negvq[(size_t)d * (ns + 1) + v] = (p - mulmod_u64((u64)v, all, p)) % p;
+        for (int v = 0; v <= ns; ++v) {
+            negvq[(size_t)d * (ns + 1) + v] = (p - mulmod_u64((u64)v, all, p)) % p;
+            negd[(size_t)d * (ns + 1) + v] = (double)negvq[(size_t)d * (ns + 1) + v];
+        }
         hd[d] = mulmod_u64((all + p - 1) % p, (p + 1) / 2, p);
     }
     upload(bc->src_mod, src); upload(bc->dst_mod, dst);
     upload(bc->inv, inv); upload(bc->mat, mat); upload(bc->negvq, negvq);
     upload(bc->half_src, hs); upload(bc->half_dst, hd);
+    upload(bc->mat_d, matd); upload(bc->negvq_d, negd);
     return *bc_cache_.emplace(std::move(key), std::move(bc)).first->second;
 }
 

@@ -27,6 +27,9 @@ struct BaseConv {
     DevBuf mat;                   // u64[ns][nd]         (Q_S/q_i) * 2^64 mod p_t   (Montgomery form)
     DevBuf negvq;                 // u64[nd][ns+1]       (-v * Q_S) mod p_t for the overflow count v
     DevBuf half_src, half_dst;    // u64[ns], u64[nd]    floor(Q_S/2) mod q_i / mod p_t
+    DevBuf mat_d, negvq_d;        // double[ns][nd], double[nd][ns+1]: the same constants in standard form, as exact
+                                  // doubles (FP64 contraction for destinations of at most 46 bits)
+    bool f64_src = false;         // every source prime has at most 46 bits
     std::vector<int> h_src, h_dst;
 };
 

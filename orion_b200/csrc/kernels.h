@@ -35,6 +35,7 @@ struct BcDev {
     int ns, nd, in_off, out_base;
     const int* src_mod; const int* dst_mod; const LimbDesc* out_off;
     const ulonglong2* inv; const u64* mat; const u64* negvq; const u64* half_src; const u64* half_dst;
+    const double* mat_d; const double* negvq_d; int f64_src;
 };
 struct BaseConvBatch { const BcDev* dev = nullptr; int n = 0; size_t smem = 0; int max_ns = 0; };
 BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& plans, const std::vector<int>& in_off,

@@ -63,6 +63,14 @@ baseconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, int ns
 // destination limbs.  The conversion's constants are staged once per CTA in shared memory, so the inner loop is
 // ns MACs + 1 REDC per output with no dependent global loads.
 constexpr int BC_TPB = 128;
+constexpr int BC_F64_BITS = 46;      // same bound as the NTT's FP64 path (ntt.cu)
+// 128-bit multiply-accumulate without the high-word reduction: every product's high word is below q/4 (y < 2^62), so
+// up to three terms stay below q * 2^64, which is all REDC needs
+__device__ __forceinline__ void mac128_raw(u64& hi, u64& lo, u64 a, u64 b) {
+    const u64 pl = a * b, ph = __umul64hi(a, b);
+    lo += pl;
+    hi += ph + (lo < pl);
+}
 template <bool CENTERED, int NS>      // NS = compile-time bound on the source-limb count of every conversion in the batch
 __global__ void __launch_bounds__(BC_TPB)
 baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
@@ -72,19 +80,24 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     const int ns = d.ns, nd = d.nd;
     u64* s_mat = (u64*)smem_raw;                       // [ns][nd]
     u64* s_neg = s_mat + ns * nd;                      // [nd][ns+1]
-    u64* s_dq = s_neg + nd * (ns + 1);                 // [nd]
+    double* s_matd = (double*)(s_neg + nd * (ns + 1)); // [ns][nd]
+    double* s_negd = s_matd + ns * nd;                 // [nd][ns+1]
+    u64* s_dq = (u64*)(s_negd + nd * (ns + 1));        // [nd]
     u64* s_dqi = s_dq + nd;                            // [nd]
     u64* s_dh = s_dqi + nd;                            // [nd]
-    u64* s_sq = s_dh + nd;                             // [ns]
+    double* s_dqinv = (double*)(s_dh + nd);            // [nd]  1/q as double; 0 marks an integer-path destination
+    u64* s_sq = (u64*)(s_dqinv + nd);                  // [ns]
     u64* s_sh = s_sq + ns;                             // [ns]
     double* s_sqd = (double*)(s_sh + ns);              // [ns]
     ulonglong2* s_inv = (ulonglong2*)(s_sqd + ns + (ns & 1));   // [ns], 16-byte aligned
     int* s_off = (int*)(s_inv + ns);                   // [nd]
-    for (int i = threadIdx.x; i < ns * nd; i += BC_TPB) s_mat[i] = d.mat[i];
-    for (int i = threadIdx.x; i < nd * (ns + 1); i += BC_TPB) s_neg[i] = d.negvq[i];
+    const bool f64 = !CENTERED && d.f64_src;
+    for (int i = threadIdx.x; i < ns * nd; i += BC_TPB) { s_mat[i] = d.mat[i]; s_matd[i] = d.mat_d[i]; }
+    for (int i = threadIdx.x; i < nd * (ns + 1); i += BC_TPB) { s_neg[i] = d.negvq[i]; s_negd[i] = d.negvq_d[i]; }
     for (int i = threadIdx.x; i < nd; i += BC_TPB) {
         const ModConst& m = mc[d.dst_mod[i]];
         s_dq[i] = m.q; s_dqi[i] = m.qinv_neg; s_dh[i] = CENTERED ? d.half_dst[i] : 0;
+        s_dqinv[i] = (f64 && m.bits <= BC_F64_BITS) ? m.qinv_d : 0.0;
         s_off[i] = d.out_base + (int)d.out_off[i].in_off;
     }
     for (int i = threadIdx.x; i < ns; i += BC_TPB) {
@@ -94,6 +107,7 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     __syncthreads();
     const int x = blockIdx.x * BC_TPB + threadIdx.x;
     u64 y[NS];
+    double yd[NS];
     double vf = 0.0;
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
@@ -103,20 +117,43 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
             if (CENTERED) xi = add_mod(xi, s_sh[i], q);
             const ulonglong2 w = s_inv[i];
             y[i] = shoup_mul(xi, w.x, w.y, q);
-            vf = __dadd_rn(vf, __ddiv_rn(__ull2double_rn(y[i]), s_sqd[i]));
+            yd[i] = __ull2double_rn(y[i]);             // exact below 2^53
+            vf = __dadd_rn(vf, __ddiv_rn(yd[i], s_sqd[i]));
         }
     }
     const u64 v = (ns == 1 && !CENTERED) ? 0 : (u64)vf;
 #pragma unroll 2
     for (int t = 0; t < nd; ++t) {
         const u64 q = s_dq[t];
-        u64 hi = 0, lo = 0;
+        const double qinv = s_dqinv[t];
+        u64 r;
+        if (!CENTERED && qinv != 0.0) {
+            // FP64 contraction (sources and destination of at most 46 bits): each product is reduced to a centred
+            // residue with 6 exact DFMA-class operations; B200 issues those at twice the rate of IMAD.WIDE
+            const double qd = __ull2double_rn(q);
+            const double M = 6755399441055744.0;
+            double acc = s_negd[t * (ns + 1) + v];
 #pragma unroll
-        for (int i = 0; i < NS; ++i)
-            if (i < ns) mac128(hi, lo, y[i], s_mat[i * nd + t], q);
-        u64 r = mont_redc(hi, lo, q, s_dqi[t]);
-        r = add_mod(r, s_neg[t * (ns + 1) + v], q);
-        if (CENTERED) r = sub_mod(r, s_dh[t], q);
+            for (int i = 0; i < NS; ++i)
+                if (i < ns) {
+                    const double w = s_matd[i * nd + t];
+                    const double h = __dmul_rn(yd[i], w), l = __fma_rn(yd[i], w, -h);
+                    const double tq = __dsub_rn(__fma_rn(h, qinv, M), M);
+                    acc = __dadd_rn(acc, __dadd_rn(__fma_rn(-tq, qd, h), l));
+                }
+            const double tq = __dsub_rn(__fma_rn(acc, qinv, M), M);
+            acc = __fma_rn(-tq, qd, acc);
+            acc = acc < 0.0 ? __dadd_rn(acc, qd) : acc;
+            r = (u64)__double_as_longlong(__dadd_rn(acc, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+        } else {
+            u64 hi = 0, lo = 0;
+#pragma unroll
+            for (int i = 0; i < NS; ++i)
+                if (i < ns) { if (NS <= 3) mac128_raw(hi, lo, y[i], s_mat[i * nd + t]); else mac128(hi, lo, y[i], s_mat[i * nd + t], q); }
+            r = mont_redc(hi, lo, q, s_dqi[t]);
+            r = add_mod(r, s_neg[t * (ns + 1) + v], q);
+            if (CENTERED) r = sub_mod(r, s_dh[t], q);
+        }
         out[(size_t)s_off[t] * N + x] = r;
     }
 }
@@ -289,9 +326,10 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
     for (size_t z = 0; z < plans.size(); ++z) {
         const BaseConv& bc = *plans[z].bc;
         h[z] = BcDev{bc.ns, bc.nd, in_off[z], out_base[z], bc.src_mod.as<int>(), bc.dst_mod.as<int>(), plans[z].out_off,
-                     bc.inv.as<ulonglong2>(), bc.mat.u(), bc.negvq.u(), bc.half_src.u(), bc.half_dst.u()};
+                     bc.inv.as<ulonglong2>(), bc.mat.u(), bc.negvq.u(), bc.half_src.u(), bc.half_dst.u(),
+                     bc.mat_d.as<double>(), bc.negvq_d.as<double>(), bc.f64_src ? 1 : 0};
         const size_t ns = bc.ns, nd = bc.nd;
-        const size_t sm = 8 * (ns * nd + nd * (ns + 1) + 3 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 4 * nd + 16;
+        const size_t sm = 8 * (2 * (ns * nd + nd * (ns + 1)) + 4 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 8 * nd + 16;
         b.smem = std::max(b.smem, sm);
         b.max_ns = std::max(b.max_ns, bc.ns);
     }
