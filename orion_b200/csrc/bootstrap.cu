@@ -126,6 +126,10 @@ struct Bootstrapper {
     std::unique_ptr<Plaintext> times_i;                  // X^(N/2) at the top level, scale 1
     scale_t built_for_scale = 0;
     u64 built_for_k = 0;
+    // encoded factors of previously seen input scales (a network bootstraps at a handful of distinct scales)
+    struct Encoded { std::vector<std::unique_ptr<LinearTransform>> cts, stc; u64 last_use = 0; };
+    std::map<scale_t, Encoded> encoded;
+    u64 use_clock = 0;
 };
 std::map<int, std::unique_ptr<Bootstrapper>>& g_boot = *new std::map<int, std::unique_ptr<Bootstrapper>>();     // keyed by slot count (LG/bootstrapper.go:16)
 
@@ -252,7 +256,25 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
     const scale_t s_mod = bs.q_at(lvl_after_cts);                            // EvalMod input scale
     const scale_t s_cheb = bs.q_at(lvl_after_cts - CHEB_DEPTH);              // Chebyshev output scale
     if (b.cts.empty() || b.built_for_scale != eff) {
+        if (!b.cts.empty()) {                                 // park the current set, keep at most 6
+            auto& e = b.encoded[b.built_for_scale];
+            e.cts = std::move(b.cts); e.stc = std::move(b.stc); e.last_use = ++b.use_clock;
+            while (b.encoded.size() > 6) {
+                auto old = b.encoded.begin();
+                for (auto i = b.encoded.begin(); i != b.encoded.end(); ++i) if (i->second.last_use < old->second.last_use) old = i;
+                b.encoded.erase(old);
+            }
+        }
         b.cts.clear(); b.stc.clear();
+        auto hit = b.encoded.find(eff);
+        if (hit != b.encoded.end()) {
+            b.cts = std::move(hit->second.cts); b.stc = std::move(hit->second.stc);
+            b.encoded.erase(hit);
+            b.built_for_scale = eff;
+        }
+    }
+    if (b.cts.empty()) {
+        if (std::getenv("ORION_B200_DEBUG")) std::fprintf(stderr, "[boot] (re)encoding DFT factors for scale %.6Lg\n", (long double)eff);
         // decoded slots after CtS must be u/(2 K'), u = coeff/(g q0); the raised ciphertext decodes to SF(coeffs)/S_r
         const double lambda = (double)((long double)q0 / (2.0L * b.K1 * g * (long double)q0));     // S_r = q0
         const double n = (double)(1 << n_log);
