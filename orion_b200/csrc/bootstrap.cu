@@ -332,8 +332,13 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
         }
         return y;
     };
-    auto vre = eval_mod(re);
-    auto vim = eval_mod(im);
+    std::unique_ptr<Ciphertext> vre, vim;
+    {
+        StreamFork f(2);                                                     // the two halves are independent chains
+        f.branch(0); vre = eval_mod(re);
+        f.branch(1); vim = eval_mod(im);
+        f.join();
+    }
     bs.mul_pt(*vim, *b.times_i, *vim);
     bs.add_ct(*vre, *vim, *ct, false);                                       // sin(2 pi u_re) + i sin(2 pi u_im)
 

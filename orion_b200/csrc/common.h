@@ -31,7 +31,24 @@ extern unsigned long long g_launches;
     kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__); ::ob::g_launches++; \
     OB_CUDA(cudaPeekAtLastError()); } while (0)
 
-cudaStream_t stream();          // the library's single compute stream
+cudaStream_t stream();          // the stream work is currently issued on (the library's main stream unless forked)
+
+// Fork / join over side streams: independent sub-computations (the two EvalMod halves of a bootstrap, the independent
+// products of a polynomial evaluation) are issued on side streams so their launch-latency-bound kernel chains overlap
+// on the GPU.  Single host thread; branch(i) switches the current stream, join() makes the parent wait for all.
+class StreamFork {
+  public:
+    explicit StreamFork(int n);
+    ~StreamFork() { join(); }
+    void branch(int i);          // subsequent work goes to side stream i (0 <= i < n)
+    void join();                 // parent stream waits for every side stream; current stream = parent again
+    int size() const { return (int)side_.size(); }
+  private:
+    cudaStream_t parent_;
+    std::vector<cudaStream_t> side_;
+    bool joined_ = false;
+};
+bool stream_fork_enabled();      // ORION_B200_STREAMS=0 disables forking (everything on one stream)
 void ensure_device();           // aborts loudly when no CUDA device is usable
 
 // stream-ordered device buffer (cudaMallocAsync pool with an unlimited release threshold -> frees are cached)

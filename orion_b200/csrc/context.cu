@@ -25,7 +25,50 @@ void ensure_device() {
     OB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
     g_dev_ok = true;
 }
-cudaStream_t stream() { ensure_device(); return g_stream; }
+static cudaStream_t g_cur = nullptr;                      // current stream while forked (single host thread by contract)
+cudaStream_t stream() { ensure_device(); return g_cur ? g_cur : g_stream; }
+
+// ---- fork / join ----
+static std::vector<cudaStream_t> g_side_pool;             // free side streams
+static std::vector<cudaEvent_t> g_event_pool;
+static cudaEvent_t take_event() {
+    if (g_event_pool.empty()) { cudaEvent_t e; OB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); return e; }
+    cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e;
+}
+bool stream_fork_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* s = std::getenv("ORION_B200_STREAMS"); on = (s && std::atoi(s) == 0) ? 0 : 1; }
+    return on == 1;
+}
+StreamFork::StreamFork(int n) : parent_(stream()) {
+    if (!stream_fork_enabled() || n <= 1) { joined_ = true; return; }
+    cudaEvent_t e = take_event();
+    OB_CUDA(cudaEventRecord(e, parent_));
+    for (int i = 0; i < n; ++i) {
+        cudaStream_t s;
+        if (g_side_pool.empty()) OB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        else { s = g_side_pool.back(); g_side_pool.pop_back(); }
+        OB_CUDA(cudaStreamWaitEvent(s, e, 0));
+        side_.push_back(s);
+    }
+    g_event_pool.push_back(e);                            // recorded events may be reused once waited on (stream-ordered)
+}
+void StreamFork::branch(int i) {
+    if (side_.empty()) return;
+    g_cur = side_[i % side_.size()];
+}
+void StreamFork::join() {
+    if (joined_) return;
+    joined_ = true;
+    for (cudaStream_t s : side_) {
+        cudaEvent_t e = take_event();
+        OB_CUDA(cudaEventRecord(e, s));
+        OB_CUDA(cudaStreamWaitEvent(parent_, e, 0));
+        g_event_pool.push_back(e);
+        g_side_pool.push_back(s);
+    }
+    g_cur = (parent_ == g_stream) ? nullptr : parent_;
+}
 
 void DevBuf::alloc(size_t n) {
     release();
@@ -34,7 +77,7 @@ void DevBuf::alloc(size_t n) {
     bytes = n;
 }
 void DevBuf::release() {
-    if (p) { cudaFreeAsync(p, g_stream); p = nullptr; bytes = 0; }
+    if (p) { cudaFreeAsync(p, g_cur ? g_cur : g_stream); p = nullptr; bytes = 0; }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -14,6 +14,7 @@
 // All constants are integers times 1, so every scale is hit exactly; the only roundings are the rescales.
 #include "polyeval.h"
 #include <cmath>
+#include <set>
 
 namespace ob {
 
@@ -55,6 +56,27 @@ struct PowerBasis {
         return *P.emplace(n, std::move(prod)).first->second;
     }
     int level_of(int n, int in_level) const { return in_level - (n <= 1 ? 0 : bitlen(n - 1)); }
+
+    // closure of the powers a set of requests will touch (same recursion as get())
+    void require(int n, std::set<int>& need) const {
+        if (n <= 1 || need.count(n)) return;
+        need.insert(n);
+        const int a = 1 << (bitlen(n - 1) - 1), b = n - a;
+        require(a, need); require(b, need);
+        if (cheb && a != b) require(a - b, need);
+    }
+    // compute every power of `need` depth by depth; the products of one depth only read shallower powers, so they are
+    // issued on side streams and overlap on the GPU
+    void precompute(const std::set<int>& need) {
+        std::map<int, std::vector<int>> by_depth;
+        for (int n : need) if (!P.count(n)) by_depth[bitlen(n - 1)].push_back(n);
+        for (auto& kv : by_depth) {
+            StreamFork f((int)std::min<size_t>(kv.second.size(), 8));
+            int i = 0;
+            for (int n : kv.second) { f.branch(i++); get(n); }
+            f.join();
+        }
+    }
 };
 
 struct Evaluator {
@@ -63,6 +85,33 @@ struct Evaluator {
     int B, in_level;
 
     bool in_basis(int n) const { return n < B || (n & (n - 1)) == 0; }
+
+    // dry run of E(): which powers will be read (same control flow, no ciphertexts)
+    void collect(const std::vector<double>& p, int L, std::set<int>& need) const {
+        int deg = (int)p.size() - 1;
+        while (deg > 0 && p[deg] == 0.0) --deg;
+        bool direct = true;
+        for (int i = 1; i <= deg; ++i)
+            if (p[i] != 0.0 && !(in_basis(i) && pb.level_of(i, in_level) >= L)) direct = false;
+        if (direct) {
+            for (int i = 1; i <= deg; ++i) if (p[i] != 0.0) pb.require(i, need);
+            return;
+        }
+        if (deg < 2) return;                                       // E() reports the error
+        const int g = 1 << (bitlen(deg) - 1);
+        pb.require(g, need);
+        std::vector<double> q(deg - g + 1, 0.0), r(p.begin(), p.begin() + g);
+        if (pb.cheb) {
+            q[0] = p[g];
+            for (int k = 1; k <= deg - g; ++k) { q[k] = 2.0 * p[g + k]; r[g - k] -= p[g + k]; }
+        } else {
+            for (int k = 0; k <= deg - g; ++k) q[k] = p[g + k];
+        }
+        if (deg != g) collect(q, L + 1, need);
+        bool r_zero = true;
+        for (double v : r) if (v != 0.0) r_zero = false;
+        if (!r_zero) collect(r, L, need);
+    }
 
     // ct at level L, scale exactly S
     std::unique_ptr<Ciphertext> E(const std::vector<double>& p, int L, scale_t S) {
@@ -108,23 +157,28 @@ struct Evaluator {
         const Ciphertext* usePg = &Pg;
         if (Pg.level > L) { pg = s.clone(Pg); s.drop_level(*pg, L); usePg = pg.get(); }
         auto res = std::make_unique<Ciphertext>();
-        if (deg == g) {                                           // q is the constant c_g: no ciphertext product needed
-            s.mul_const_scaled(*usePg, q[0], S / Pg.scale, *res);
-        } else {
-            OB_CHECK(L + 1 <= in_level, "polynomial evaluation: not enough levels for this degree");
-            const scale_t qS = (S / Pg.scale) * s.q_at(L + 1);
-            auto A = E(q, L + 1, qS);
-            s.rescale(*A, *A);
-            A->scale = S / Pg.scale;
-            s.mul_relin(*A, *usePg, *res);
-        }
-        res->scale = S;
         bool r_zero = true;
         for (double v : r) if (v != 0.0) r_zero = false;
-        if (!r_zero) {
-            auto R = E(r, L, S);
-            s.add_ct(*res, *R, *res, false);
+        std::unique_ptr<Ciphertext> R;
+        {
+            // quotient branch and remainder branch are independent: two side streams
+            StreamFork f((deg != g && !r_zero) ? 2 : 1);
+            f.branch(0);
+            if (deg == g) {                                       // q is the constant c_g: no ciphertext product needed
+                s.mul_const_scaled(*usePg, q[0], S / Pg.scale, *res);
+            } else {
+                OB_CHECK(L + 1 <= in_level, "polynomial evaluation: not enough levels for this degree");
+                const scale_t qS = (S / Pg.scale) * s.q_at(L + 1);
+                auto A = E(q, L + 1, qS);
+                s.rescale(*A, *A);
+                A->scale = S / Pg.scale;
+                s.mul_relin(*A, *usePg, *res);
+            }
+            res->scale = S;
+            if (!r_zero) { f.branch(1); R = E(r, L, S); }
+            f.join();
         }
+        if (!r_zero) s.add_ct(*res, *R, *res, false);
         return res;
     }
 };
@@ -145,6 +199,11 @@ std::unique_ptr<Ciphertext> poly_evaluate(Scheme& s, const Ciphertext& in, const
     pb.P[1] = s.clone(in);
     Evaluator ev{s, pb, 1 << ((depth + 1) / 2), in.level};
     std::vector<double> c(poly.coeffs.begin(), poly.coeffs.begin() + d + 1);
+    {
+        std::set<int> need;
+        ev.collect(c, out_level + 1, need);
+        pb.precompute(need);
+    }
     auto res = ev.E(c, out_level + 1, out_scale * s.q_at(out_level + 1));
     s.rescale(*res, *res);
     res->scale = out_scale;
