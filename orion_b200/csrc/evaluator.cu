@@ -161,8 +161,11 @@ void PolyEvaluator::keyswitch_n(int level, int n, const u64* c1s, int c1_zstride
                                 int addend_zstride, u64* out) {
     const KsPlan& p = ks_plan(level);
     const size_t N = ctx.N, dw = digits_words(level);
-    for (int z0 = 0; z0 < n; z0 += IPM_MAX) {
-        const int m = std::min(IPM_MAX, n - z0);
+    // ciphertexts per launch sequence: enough to fill the GPU in the short kernels, small enough that the digit buffers
+    // (beta*W limbs each) stay around 1 GB -- larger working sets measured slower (profiles/: batch 64 at logN=16, L=24)
+    const int chunk = (int)std::max<size_t>(4, std::min<size_t>(IPM_MAX, ((size_t)1 << 30) / (dw * 8)));
+    for (int z0 = 0; z0 < n; z0 += chunk) {
+        const int m = std::min(chunk, n - z0);
         DevBuf digits((size_t)m * dw * 8), acc((size_t)m * 2 * p.W * N * 8);
         const u64* c1 = c1s + (size_t)z0 * c1_zstride * N;
         decompose_n(level, c1, c1_zstride, m, digits.u());

@@ -21,8 +21,8 @@ namespace ob {
 
 namespace {
 
-constexpr int LOG_E_STRIDED = 12;   // 4096 words per tile, 512 threads
-constexpr int LOG_E_CONTIG = 11;    // 2048 words per tile, 256 threads
+constexpr int LOG_E_STRIDED = 11;   // 2048 words per tile, 256 threads
+constexpr int LOG_E_CONTIG = 10;    // 1024 words per tile, 128 threads
 constexpr int K2_BITS = 8;          // contiguous pass handles the 8 low index bits
 
 __device__ __forceinline__ int insert_bits(int x, int pos, int nb, int v) {
