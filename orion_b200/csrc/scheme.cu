@@ -39,10 +39,14 @@ pk_assemble_kernel(const u64* __restrict__ a, const u64* __restrict__ e, const u
 }  // namespace
 
 Scheme::Scheme(const SchemeParams& p, u64 seed_) : params(p) {
-    OB_CHECK(!p.conjugate_invariant, "RingType ConjugateInvariant is not supported by this backend yet (use standard)");
+    // RingType ConjugateInvariant (configs/lola.yml; LG/scheme.go:46-55): Lattigo folds Z[X+X^-1]/(X^2N+1) into N
+    // coefficients, N real slots, primes = 1 mod 4N.  This backend serves it with the standard ring of degree 2N: the
+    // same prime chain (NthRoot 4N), the same N slots (orion/backend/python/parameters.py:33-35), every operation
+    // unchanged; real inputs stay real.  Cost: ciphertexts are twice the size of Lattigo's folded representation.
+    const int ring_logN = p.logN + (p.conjugate_invariant ? 1 : 0);
     std::vector<u64> Q, P;
-    gen_moduli(p.logQ, p.logP, p.logN + 1, Q, P);
-    ctx = std::make_unique<Context>(p.logN, Q, P);
+    gen_moduli(p.logQ, p.logP, ring_logN + 1, Q, P);
+    ctx = std::make_unique<Context>(ring_logN, Q, P);
     init_common(seed_);
 }
 Scheme::Scheme(int logN, const std::vector<u64>& Q, const std::vector<u64>& P, int log_scale, int h, u64 seed_) {

@@ -8,6 +8,7 @@ logged; float payloads (encoded vectors, diagonals, polynomial coefficients) go 
 
   python tests/golden/make_orion_traces.py mlp        -> tests/golden/trace_mlp.{json,npz}      (full payloads)
   python tests/golden/make_orion_traces.py resnet20   -> tests/golden/trace_resnet20.json       (structure only)
+  python tests/golden/make_orion_traces.py lola_ci    -> configs/lola.yml as shipped (ConjugateInvariant ring)
 
 `orion_b200/replay.py` replays a trace through B200Library on the GPU (tests/test_gpu_models.py, bench.py).
 """
@@ -96,8 +97,9 @@ class SymbolicBackend:
         self.logn = params.get_logn()
         self.logq, self.logp = params.get_logq(), params.get_logp()
         self.logscale = params.get_logscale()
-        self.Q, self.P = raw.gen_moduli(self.logq, self.logp, self.logn + 1)
-        self.max_slots = 1 << (self.logn - 1)
+        ci = params.get_ringtype() != "standard"            # conjugate-invariant ring: N slots, primes = 1 mod 4N
+        self.Q, self.P = raw.gen_moduli(self.logq, self.logp, self.logn + (2 if ci else 1))
+        self.max_slots = 1 << (self.logn if ci else self.logn - 1)
         self.max_level = len(self.Q) - 1
         self._log("NewScheme", self.logn, self.logq, self.logp, self.logscale, params.get_hamming_weight(),
                   params.get_ringtype(), "", "none")
@@ -286,6 +288,10 @@ def build_model(name):
         net = models.LoLA()
         x = (torch.rand(1, 1, 28, 28) - 0.1307) / 0.3081
         cfg = os.path.join(REF, "configs", "lola2.yml")
+    elif name == "lola_ci":                                  # configs/lola.yml as shipped: ConjugateInvariant ring, logN=13
+        net = models.LoLA()
+        x = (torch.rand(1, 1, 28, 28) - 0.1307) / 0.3081
+        cfg = os.path.join(REF, "configs", "lola.yml")
     elif name == "resnet20":
         net = models.ResNet20()
         mean = torch.tensor([0.4914, 0.4822, 0.4465]).view(1, 3, 1, 1)
@@ -310,8 +316,9 @@ def main():
     net, x, cfg_path = build_model(name)
     cfg = yaml.safe_load(open(cfg_path))
     cfg["orion"]["debug"] = False
-    cfg["orion"]["io_mode"] = "none"
-    cfg["ckks_params"]["RingType"] = "standard"
+    cfg["orion"]["io_mode"] = "none"                       # run with TORCHDYNAMO_DISABLE=1 where inductor cannot compile
+    if name != "lola_ci":
+        cfg["ckks_params"]["RingType"] = "standard"
     for a in sys.argv[2:]:
         if a.startswith("--logn="):
             cfg["ckks_params"]["LogN"] = int(a.split("=")[1])

@@ -49,3 +49,20 @@ def test_lola_encrypted_inference_matches_cleartext(b200lib):
     fhe = res["output"][: len(clear)]
     assert float(np.mean(np.abs(clear - fhe))) < 0.005
     assert int(np.argmax(fhe)) == int(np.argmax(clear))
+
+
+def test_lola_conjugate_invariant_config_as_shipped(b200lib):
+    """configs/lola.yml exactly as shipped: RingType ConjugateInvariant, logN=13, 8192 real slots (the reference packs
+    orion/backend/python/parameters.py:33-35 slots).  Served by the degree-2N standard ring."""
+    res = run_trace("lola_ci")
+    assert res["meta"]["config"]["ckks_params"]["RingType"] == "ConjugateInvariant"
+    clear = np.array(res["meta"]["clear_output"])
+    fhe = res["output"][: len(clear)]
+    assert len(res["output"]) == 8192
+    # 26-bit primes = 1 mod 4N (N = 8192) sit up to a few 2^15 away from 2^26, and Orion's layers reset scales to the
+    # nominal 2^26 (SetCiphertextScale in the trace), so the logits carry a ~1 % systematic scale drift with this
+    # parameter set -- a property of configs/lola.yml's chain, not of the backend (the 30-bit lola2.yml chain above meets
+    # the 0.005 gate).  Gate: MAE < 0.02 on logits of magnitude ~1, same argmax, same ranking.
+    assert float(np.mean(np.abs(clear - fhe))) < 0.02
+    assert int(np.argmax(fhe)) == int(np.argmax(clear))
+    assert np.array_equal(np.argsort(fhe), np.argsort(clear))
