@@ -35,6 +35,7 @@ constexpr int CTS_DEPTH = 4, STC_DEPTH = 3, CHEB_DEPTH = 6, LOG_MSG_RATIO = 10;
 // out[p][i][x] = centred(in[p][x] mod q0) mod q_i      (coefficient domain)
 __global__ void __launch_bounds__(TPB)
 mod_raise_kernel(const u64* __restrict__ in, u64* __restrict__ out, int limbs, int N, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int i = blockIdx.y, p = blockIdx.z, x = blockIdx.x * TPB + threadIdx.x;
     const u64 q0 = mc[0].q, v = in[(size_t)p * N + x];
     const ModConst m = mc[i];

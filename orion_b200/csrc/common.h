@@ -27,9 +27,28 @@ namespace ob {
 
 // launch counter: every kernel of this library goes through OB_LAUNCH so bench.py can report gpu_launches
 extern unsigned long long g_launches;
+// Launches can be programmatic dependent launches (PDL): the next kernel of the stream may be scheduled while this one
+// drains, and blocks in OB_PDL_SYNC() -- the first statement of EVERY kernel of this library -- until its predecessor has
+// completed and flushed.  Overlaps the tail wave of large kernels with the head of the next; policy in context.cu
+// (pdl_enabled: on for logN >= 15, ORION_B200_PDL=0/1 overrides).
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    OB_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+}
 #define OB_LAUNCH(kernel, grid, block, smem, stream, ...) do { \
-    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__); ::ob::g_launches++; \
-    OB_CUDA(cudaPeekAtLastError()); } while (0)
+    ::ob::launch_kernel(kernel, dim3(grid), dim3(block), (size_t)(smem), (stream), __VA_ARGS__); ::ob::g_launches++; } while (0)
+#ifdef __CUDACC__
+// griddepcontrol.launch_dependents: the dependent grid may start launching once every CTA of this grid got here;
+// griddepcontrol.wait: block until the grid this one depends on has completed (memory visible).
+#define OB_PDL_SYNC() do { asm volatile("griddepcontrol.launch_dependents;"); asm volatile("griddepcontrol.wait;" ::: "memory"); } while (0)
+#endif
 
 cudaStream_t stream();          // the stream work is currently issued on (the library's main stream unless forked)
 

@@ -35,6 +35,15 @@ static cudaEvent_t take_event() {
     if (g_event_pool.empty()) { cudaEvent_t e; OB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); return e; }
     cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e;
 }
+// PDL policy: measured +3 % on the logN=16 key switch (tail of one kernel overlaps the head of the next) and -30 % on a
+// bare rescale chain, but -9 % on the ResNet-20 replay at logN=13, where early-resident dependents take SM slots from
+// the side streams' kernels.  Default: on for rings of degree >= 2^15, off below; ORION_B200_PDL=0/1 overrides.
+static bool g_pdl_auto = false;
+bool pdl_enabled() {
+    static int forced = -2;
+    if (forced == -2) { const char* s = std::getenv("ORION_B200_PDL"); forced = s ? (std::atoi(s) != 0) : -1; }
+    return forced >= 0 ? forced == 1 : g_pdl_auto;
+}
 bool stream_fork_enabled() {
     static int on = -1;
     if (on < 0) { const char* s = std::getenv("ORION_B200_STREAMS"); on = (s && std::atoi(s) == 0) ? 0 : 1; }
@@ -220,6 +229,7 @@ static void upload(DevBuf& d, const std::vector<T>& h) {
 Context::Context(int logN_, const std::vector<u64>& Q, const std::vector<u64>& P) {
     ensure_device();
     logN = logN_; N = 1 << logN; nQ = (int)Q.size(); nP = (int)P.size(); nmod = nQ + nP;
+    g_pdl_auto = logN >= 15;
     OB_CHECK(logN >= 10 && logN <= 17, "logN must be within 10..17");
     OB_CHECK(nmod <= 64, "at most 64 moduli");
     mod = Q; mod.insert(mod.end(), P.begin(), P.end());

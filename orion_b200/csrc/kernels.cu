@@ -23,6 +23,7 @@ __global__ void __launch_bounds__(TPB)
 ew_binary_kernel(const u64* __restrict__ a, int a_stride, const u64* __restrict__ b, int b_stride, int b_polys,
                  u64* __restrict__ out, int out_stride, int limbs, int L, int nQ, int N,
                  const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, p = blockIdx.z;
     const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
     if (x >= N) return;
@@ -45,6 +46,7 @@ template <int MODE>
 __global__ void __launch_bounds__(TPB)
 ew_scalar_kernel(const u64* __restrict__ a, int a_stride, u64* __restrict__ out, int out_stride, int L, int nQ, int N,
                  const ModConst* __restrict__ mc, const ulonglong2* __restrict__ scal, int only_poly) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, p = blockIdx.z;
     const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
     if (x >= N) return;
@@ -59,6 +61,7 @@ ew_scalar_kernel(const u64* __restrict__ a, int a_stride, u64* __restrict__ out,
 __global__ void __launch_bounds__(TPB)
 tensor_kernel(const u64* __restrict__ a, int a_stride, const u64* __restrict__ b, int b_stride,
               u64* __restrict__ out, int L, int N, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y;
     const int x = blockIdx.x * TPB + threadIdx.x;
     const ModConst m = mc[t];
@@ -75,6 +78,7 @@ tensor_kernel(const u64* __restrict__ a, int a_stride, const u64* __restrict__ b
 
 __global__ void __launch_bounds__(TPB)
 automorphism_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const uint32_t* __restrict__ idx) {
+    OB_PDL_SYNC();
     const int x = blockIdx.x * TPB + threadIdx.x;
     const size_t base = (size_t)blockIdx.y * N;
     out[base + x] = in[base + __ldg(&idx[x])];
@@ -84,6 +88,7 @@ template <bool TO>
 __global__ void __launch_bounds__(TPB)
 mont_kernel(const u64* __restrict__ in, u64* __restrict__ out, int limbs, int L, int nQ, int N,
             const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, p = blockIdx.z;
     const int x = blockIdx.x * TPB + threadIdx.x;
     const ModConst m = mc[chain_of(t, L, nQ)];

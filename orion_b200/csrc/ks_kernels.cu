@@ -25,6 +25,7 @@ baseconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, int ns
                 const ulonglong2* __restrict__ inv, const u64* __restrict__ mat, const u64* __restrict__ negvq,
                 const u64* __restrict__ half_src, const u64* __restrict__ half_dst,
                 const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int x = blockIdx.x * TPB + threadIdx.x;
     u64 y[MAX_NS];
     double vf = 0.0;
@@ -75,6 +76,7 @@ template <bool CENTERED, int NS>      // NS = compile-time bound on the source-l
 __global__ void __launch_bounds__(BC_TPB)
 baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                       const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const BcDev d = descs[blockIdx.y];
     const int ns = d.ns, nd = d.nd;
@@ -164,6 +166,7 @@ __global__ void __launch_bounds__(TPB)
 inner_product_kernel(const u64* __restrict__ c1, const u64* __restrict__ digits, const u64* __restrict__ evk,
                      u64* __restrict__ acc, int N, int L, int K, int nQ, int nmod, int beta,
                      const uint32_t* __restrict__ gather, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, W = L + K;
     const int x = blockIdx.x * TPB + threadIdx.x;
     const int ci = t < L ? t : nQ + (t - L);
@@ -197,6 +200,7 @@ inner_product_multi_kernel(const u64* __restrict__ c1, size_t c1_zstride, const 
                            const u64* __restrict__ addend, size_t addend_zstride,
                            int N, int L, int K, int nQ, int nmod, int beta,
                            const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, z = blockIdx.z, W = L + K;
     const int x = blockIdx.x * TPB + threadIdx.x;
     const int ci = t < L ? t : nQ + (t - L);
@@ -228,6 +232,7 @@ inner_product_multi_kernel(const u64* __restrict__ c1, size_t c1_zstride, const 
 // out[p][t][x] = sum_z in[z][p][t][x]  (mod q_t), QP layout with W limbs per polynomial
 __global__ void __launch_bounds__(TPB)
 sum_qp_kernel(const SumList lst, int n, u64* __restrict__ out, int N, int L, int W, int nQ, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, p = blockIdx.z;
     const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
     const u64 q = mc[t < L ? t : nQ + (t - L)].q;
@@ -245,6 +250,7 @@ moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __
                       const u64* __restrict__ addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
                       u64* __restrict__ out, int out_stride, int N,
                       const ulonglong2* __restrict__ pinv, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int i = blockIdx.y, p = blockIdx.z;
     const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
     const u64 q = mc[i].q;
@@ -267,6 +273,7 @@ moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __
 __global__ void __launch_bounds__(TPB)
 rescale_prep_kernel(const u64* __restrict__ last, u64* __restrict__ tmp, int level, int N,
                     const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int i = blockIdx.y, p = blockIdx.z;
     const int x = blockIdx.x * TPB + threadIdx.x;
     const u64 ql = mc[level].q, half = (ql - 1) >> 1;
@@ -280,6 +287,7 @@ __global__ void __launch_bounds__(TPB)
 rescale_finish_kernel(const u64* __restrict__ in, int in_stride, const u64* __restrict__ tmp,
                       u64* __restrict__ out, int out_stride, int level, int N,
                       const ulonglong2* __restrict__ qlinv_row, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int i = blockIdx.y, p = blockIdx.z;
     const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
     const u64 q = mc[i].q;

@@ -28,6 +28,7 @@ struct LtMacMulti { const int2* pairs[LTM_MAX]; int np[LTM_MAX]; };
 __global__ void __launch_bounds__(TPB)
 lt_mac_kernel(const u64* __restrict__ diags, const u64* __restrict__ rots, const LtMacMulti mm, u64* __restrict__ acc_all,
               int N, int L, int W, int L_lt, int W_lt, int nQ, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x, z = blockIdx.z;
     const int ci = t < L ? t : nQ + (t - L);
     const int td = t < L ? t : L_lt + (t - L);
@@ -51,6 +52,7 @@ lt_mac_kernel(const u64* __restrict__ diags, const u64* __restrict__ rots, const
 __global__ void __launch_bounds__(TPB)
 lift_times_p_kernel(const u64* __restrict__ c, int c_stride, u64* __restrict__ out, int N, int L, int W,
                     const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, p = blockIdx.z, x = blockIdx.x * TPB + threadIdx.x;
     u64 v = 0;
     if (t < L) { const ulonglong2 w = pmodq[t]; v = shoup_mul(c[((size_t)p * c_stride + t) * N + x], w.x, w.y, mc[t].q); }
@@ -60,6 +62,7 @@ lift_times_p_kernel(const u64* __restrict__ c, int c_stride, u64* __restrict__ o
 __global__ void __launch_bounds__(TPB)
 add_times_p_kernel(u64* __restrict__ acc, const u64* __restrict__ c, int N,
                    const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
     const u64 q = mc[t].q; const ulonglong2 w = pmodq[t];
     const size_t o = (size_t)t * N + x;

@@ -249,6 +249,7 @@ __global__ void __launch_bounds__(1 << (LOG_E - 3))
 ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
          const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all,
          const ulonglong2* __restrict__ ninv_all, int logN) {
+    OB_PDL_SYNC();
     __shared__ __align__(16) u64 sm[1 << LOG_E];
     const LimbDesc ld = limbs[blockIdx.y];
     const size_t N = (size_t)1 << logN;

@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(TPB)
 evk_assemble_kernel(const u64* __restrict__ a, const u64* __restrict__ e, const u64* __restrict__ s_out,
                     const u64* __restrict__ s_in, const ulonglong2* __restrict__ pmodq, int own_lo, int own_hi,
                     u64* __restrict__ out_b, u64* __restrict__ out_a, int N, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
     const ModConst m = mc[t];
     const size_t o = (size_t)t * N + x;
@@ -31,6 +32,7 @@ evk_assemble_kernel(const u64* __restrict__ a, const u64* __restrict__ e, const 
 __global__ void __launch_bounds__(TPB)
 pk_assemble_kernel(const u64* __restrict__ a, const u64* __restrict__ e, const u64* __restrict__ s,
                    u64* __restrict__ out_b, int N, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
     const ModConst m = mc[t];
     const size_t o = (size_t)t * N + x;

@@ -22,6 +22,7 @@ __constant__ u64 c_gauss_cdt[20] = {
 __global__ void __launch_bounds__(TPB)
 uniform_kernel(u64* __restrict__ out, int N, const LimbDesc* __restrict__ limbs, const ModConst* __restrict__ mc,
                u64 seed, u64 stream0) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
     const ModConst& m = mc[limbs[t].mod];
     const u64 q = m.q, mask = m.bits >= 64 ? ~0ull : ((1ull << m.bits) - 1);
@@ -32,6 +33,7 @@ uniform_kernel(u64* __restrict__ out, int N, const LimbDesc* __restrict__ limbs,
 
 __global__ void __launch_bounds__(TPB)
 gaussian_kernel(int64_t* __restrict__ out, u64 seed, u64 stream) {
+    OB_PDL_SYNC();
     const int x = blockIdx.x * TPB + threadIdx.x;
     const u64 r = rng_u64(seed, stream, (u64)x), s = rng_u64(seed, stream, (1ull << 32) | (u64)x);
     int k = 0;
@@ -42,6 +44,7 @@ gaussian_kernel(int64_t* __restrict__ out, u64 seed, u64 stream) {
 __global__ void __launch_bounds__(TPB)
 small_to_rns_kernel(const int64_t* __restrict__ small, u64* __restrict__ out, int N,
                     const LimbDesc* __restrict__ limbs, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
     const ModConst m = mc[limbs[t].mod];
     const int64_t v = small[x];
@@ -58,6 +61,7 @@ __device__ __forceinline__ double2 cmul(double2 a, double2 b) {
 __global__ void __launch_bounds__(TPB)
 ifft_stage_kernel(double2* __restrict__ vals, int slots, int len, int M, const double2* __restrict__ roots,
                   const int* __restrict__ rot) {
+    OB_PDL_SYNC();
     const int b = blockIdx.x * TPB + threadIdx.x;
     if (b >= slots / 2) return;
     double2* v = vals + (size_t)blockIdx.y * slots;
@@ -72,6 +76,7 @@ ifft_stage_kernel(double2* __restrict__ vals, int slots, int len, int M, const d
 __global__ void __launch_bounds__(TPB)
 fft_stage_kernel(double2* __restrict__ vals, int slots, int len, int M, const double2* __restrict__ roots,
                  const int* __restrict__ rot) {
+    OB_PDL_SYNC();
     const int b = blockIdx.x * TPB + threadIdx.x;
     if (b >= slots / 2) return;
     double2* v = vals + (size_t)blockIdx.y * slots;
@@ -85,6 +90,7 @@ fft_stage_kernel(double2* __restrict__ vals, int slots, int len, int M, const do
 // bit-reversal permutation (in place, pairwise swap), optionally dividing by `div`
 __global__ void __launch_bounds__(TPB)
 bitrev_scale_kernel(double2* __restrict__ vals, int slots, int log_slots, double div) {
+    OB_PDL_SYNC();
     const int i = blockIdx.x * TPB + threadIdx.x;
     if (i >= slots) return;
     double2* v = vals + (size_t)blockIdx.y * slots;
@@ -112,6 +118,7 @@ __device__ __forceinline__ u64 double_to_mod(double x, const ModConst& m) {
 __global__ void __launch_bounds__(TPB)
 encode_round_kernel(const double2* __restrict__ vals, int log_slots, double scale, u64* __restrict__ coeffs,
                     int N, int nlimbs, const LimbDesc* __restrict__ limbs, const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
     const int c = blockIdx.x * TPB + threadIdx.x;      // coefficient index
     const int bidx = blockIdx.y;                       // vector in the batch
     const int slots = 1 << log_slots, half = N >> 1, gap = half >> log_slots;
@@ -137,6 +144,7 @@ __global__ void __launch_bounds__(128)
 decode_crt_kernel(const u64* __restrict__ coeffs, int L, int nQ, int N, double inv_scale_num, double2* __restrict__ vals,
                   int log_slots, const ulonglong2* __restrict__ qinv /* [j][i] = q_j^-1 mod q_i */,
                   const ModConst* __restrict__ mc, const double* __restrict__ pd) {
+    OB_PDL_SYNC();
     const int s = blockIdx.x * 128 + threadIdx.x;
     const int slots = 1 << log_slots, half = N >> 1, gap = half >> log_slots;
     if (s >= 2 * slots) return;
