@@ -240,6 +240,11 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ntt_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
     ntt_gbs = ntt_bytes / (ntt_ms * 1e-3) / 1e9
 
     total_ks = BATCH * args.steps * world
@@ -278,7 +283,8 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "ntt_pass (forward NTT of the %d converted digit limbs, 2 launches)" % nl,
                          "achieved": ntt_gbs, "peak": peak, "unit": "GB/s", "frac": ntt_gbs / peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                         "traffic": None},
+                         "algorithmic_bytes_per_launch": ntt_bytes // 2, "launches": 2,
+                         "traffic": traffic, "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture (profiles/ntt_traffic.json)"},
             "clocks": clocks,
         }
         if cpu:
