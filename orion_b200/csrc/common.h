@@ -32,8 +32,10 @@ extern unsigned long long g_launches;
 // completed and flushed.  Overlaps the tail wave of large kernels with the head of the next; policy in context.cu
 // (pdl_enabled: on for logN >= 15, ORION_B200_PDL=0/1 overrides).
 bool pdl_enabled();
+bool dry_run();        // ORION_B200_DRYRUN=1: skip the launches (host-side enqueue cost measurement only; results are garbage)
 template <class... KArgs, class... Args>
 inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    if (dry_run()) return;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];

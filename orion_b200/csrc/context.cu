@@ -44,6 +44,11 @@ bool pdl_enabled() {
     if (forced == -2) { const char* s = std::getenv("ORION_B200_PDL"); forced = s ? (std::atoi(s) != 0) : -1; }
     return forced >= 0 ? forced == 1 : g_pdl_auto;
 }
+bool dry_run() {
+    static int on = -1;
+    if (on < 0) { const char* s = std::getenv("ORION_B200_DRYRUN"); on = (s && std::atoi(s) != 0) ? 1 : 0; }
+    return on == 1;
+}
 bool stream_fork_enabled() {
     static int on = -1;
     if (on < 0) { const char* s = std::getenv("ORION_B200_STREAMS"); on = (s && std::atoi(s) == 0) ? 0 : 1; }
