@@ -28,8 +28,11 @@ constexpr int K2_BITS = 8;          // contiguous pass handles the 8 low index b
 __device__ __forceinline__ int insert_bits(int x, int pos, int nb, int v) {
     return ((x >> pos) << (pos + nb)) | (v << pos) | (x & ((1 << pos) - 1));
 }
-// bijection on the low 4 bits: keeps 64-bit shared-memory accesses conflict-free for all round shapes
-__device__ __forceinline__ int swz(int li) { return li ^ ((li >> 4) & 3) ^ (((li >> 5) & 3) << 2); }
+// Shared-memory layout: word li of a tile lives at pad(li) = li + (li >> 4) + 2 (li >> 5).  Same bank behaviour as an
+// XOR swizzle of the low index bits for every round shape (brute-forced on the host), but ADDITIVE: for the 8 words a
+// thread owns in a round, li = base | (k << pos) with the k bits of base zero, so pad(li) = pad(base) + pad(k << pos)
+// exactly (no carries) -- one address computation per thread and round, compile-time offsets for the rest.
+__host__ __device__ constexpr int pad(int li) { return li + (li >> 4) + ((li >> 5) << 1); }
 
 // ---- arithmetic policies ------------------------------------------------------------------------------------
 // ArithInt : Harvey lazy butterflies on u64 with Shoup twiddles (any prime < 2^62).  6 IMAD.WIDE + 4 IMAD per
@@ -178,6 +181,7 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
     };
 
     constexpr int NR = (NBITS + 2) / 3, RBASE = NBITS / NR, REXTRA = NBITS % NR;
+    const int row_stride = 1 << (logN - nbits);          // STRIDED: distance between consecutive tile rows in the limb
     int done = 0;
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
@@ -188,33 +192,41 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
         // which register pairs sit in adjacent words (-> 128-bit global accesses): with pos == 0 elements e, e+1;
         // with pos > 0 and G >= 2 the same k of groups g, g+1 (bit 0 of the local index is bit 0 of g)
         const int pair_step = pos == 0 ? 1 : (G >= 2 ? (1 << nb) : 0);
-        T v[8]; int li[8]; int twb[8];
+        // per group g: local index with the round's k bits zero, its shared-memory slot and its word index in the limb;
+        // element (g, k) adds compile-time offsets to both
+        T v[8]; int sbase[8], gbase[8], twb[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            int g = e >> nb, k = e & ((1 << nb) - 1);
-            li[e] = insert_bits(tid * G + g, pos, nb, k);
-        }
-#pragma unroll
-        for (int g = 0; g < 8; ++g)
+        for (int g = 0; g < 8; ++g) {
+            if (g < G) {
+                const int base = insert_bits(tid * G + g, pos, nb, 0);
+                sbase[g] = pad(base);
+                gbase[g] = gidx(base);
+            }
             twb[g] = (1 << (TOP - ptop)) + ((tid * G + g) >> pos) + (tile_base >> (ptop + 1));
+        }
+        auto soff = [&](int e) { return sbase[e >> nb] + pad((e & ((1 << nb) - 1)) << pos); };
+        auto goff = [&](int e) {
+            const int k = e & ((1 << nb) - 1);
+            return gbase[e >> nb] + (STRIDED ? (k << (pos - logC)) * row_stride : (k << pos));
+        };
         if (r == 0) {
             u64 w[8];
             if (pair_step) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e)
                     if (!(e & pair_step)) {
-                        const ulonglong2 t = *(const ulonglong2*)(src + gidx(li[e]));
+                        const ulonglong2 t = *(const ulonglong2*)(src + goff(e));
                         w[e] = t.x; w[e + pair_step] = t.y;
                     }
             } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) w[e] = src[gidx(li[e])];
+                for (int e = 0; e < 8; ++e) w[e] = src[goff(e)];
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = FINAL ? ar.from_raw(w[e]) : ar.from_word(w[e]);
         } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = ar.from_raw(sm[swz(li[e])]);
+            for (int e = 0; e < 8; ++e) v[e] = ar.from_raw(sm[soff(e)]);
         }
         if (FWD) {
             if (nb == 3) fwd_radix<3>(ar, v, tw, twb); else if (nb == 2) fwd_radix<2>(ar, v, tw, twb); else fwd_radix<1>(ar, v, tw, twb);
@@ -231,14 +243,14 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
             if (pair_step) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e)
-                    if (!(e & pair_step)) *(ulonglong2*)(dst + gidx(li[e])) = make_ulonglong2(w[e], w[e + pair_step]);
+                    if (!(e & pair_step)) *(ulonglong2*)(dst + goff(e)) = make_ulonglong2(w[e], w[e + pair_step]);
             } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) dst[gidx(li[e])] = w[e];
+                for (int e = 0; e < 8; ++e) dst[goff(e)] = w[e];
             }
         } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) sm[swz(li[e])] = ar.to_raw(v[e]);
+            for (int e = 0; e < 8; ++e) sm[soff(e)] = ar.to_raw(v[e]);
             __syncthreads();
         }
     }
@@ -250,7 +262,7 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
          const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all,
          const ulonglong2* __restrict__ ninv_all, int logN) {
     OB_PDL_SYNC();
-    __shared__ __align__(16) u64 sm[1 << LOG_E];
+    __shared__ __align__(16) u64 sm[(1 << LOG_E) + (1 << (LOG_E - 3))];      // padded layout, see pad()
     const LimbDesc ld = limbs[blockIdx.y];
     const size_t N = (size_t)1 << logN;
     const ModConst& m = mc[ld.mod];
