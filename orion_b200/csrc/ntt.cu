@@ -32,7 +32,12 @@ __device__ __forceinline__ int insert_bits(int x, int pos, int nb, int v) {
 // XOR swizzle of the low index bits for every round shape (brute-forced on the host), but ADDITIVE: for the 8 words a
 // thread owns in a round, li = base | (k << pos) with the k bits of base zero, so pad(li) = pad(base) + pad(k << pos)
 // exactly (no carries) -- one address computation per thread and round, compile-time offsets for the rest.
-__host__ __device__ constexpr int pad(int li) { return li + (li >> 4) + ((li >> 5) << 1); }
+// Coefficients per thread (LOG_EPT): 16 in the strided pass (radix-16 rounds: ONE exchange per 8 stages, measured 58 -> 48 us
+// on 192 limbs), 8 in the contiguous pass (16 there means 128-byte-strided stores and twiddle loads: measured slower).
+// The inverse strided pass (final, N^-1 scaling) measured slower with 16 (63 -> 107 us), so it keeps 8 as well.
+__host__ __device__ constexpr int log_ept(bool strided, bool fwd) { return (strided && fwd) ? 4 : 3; }
+template <int LOG_EPT>
+__host__ __device__ constexpr int pad(int li) { return LOG_EPT == 4 ? li + (li >> 4) : li + (li >> 4) + ((li >> 5) << 1); }
 
 // ---- arithmetic policies ------------------------------------------------------------------------------------
 // ArithInt : Harvey lazy butterflies on u64 with Shoup twiddles (any prime < 2^62).  6 IMAD.WIDE + 4 IMAD per
@@ -60,6 +65,7 @@ struct ArithInt {
     __device__ __forceinline__ T from_raw(u64 x) const { return x; }           // inter-pass / shared-memory word
     __device__ __forceinline__ u64 to_raw(T x) const { return x; }
     __device__ __forceinline__ TW ldtw(const TW* p) const { return __ldg(p); }
+    __device__ __forceinline__ void ldtw2(const TW* p, TW& a, TW& b) const { a = __ldg(p); b = __ldg(p + 1); }
     __device__ __forceinline__ void ct(T& a, T& b, TW w) const {
         u64 x = a >= q2 ? a - q2 : a;                 // [0,2q)
         u64 v = shoup_lazy(b, w.x, w.y, q);           // [0,2q)
@@ -86,6 +92,8 @@ struct ArithF64 {
     __device__ __forceinline__ T from_raw(u64 x) const { return __longlong_as_double(x); }
     __device__ __forceinline__ u64 to_raw(T x) const { return (u64)__double_as_longlong(x); }
     __device__ __forceinline__ TW ldtw(const TW* p) const { return __ldg(p); }
+    // two consecutive twiddles (even index) as one 128-bit load: halves the sector requests of the late stages
+    __device__ __forceinline__ void ldtw2(const TW* p, TW& a, TW& b) const { const double2 t = __ldg((const double2*)p); a = t.x; b = t.y; }
     __device__ __forceinline__ T mulmod(T x, T w) const {                     // centred residue of x*w, |r| <= 0.7q
         const double h = __dmul_rn(x, w), l = __fma_rn(x, w, -h);
         const double t = __dsub_rn(__fma_rn(h, qinv, F64_MAGIC), F64_MAGIC);
@@ -111,43 +119,53 @@ struct ArithF64 {
     __device__ __forceinline__ u64 final_inv(T x, ulonglong2 ni) const { return to_word(mulmod(x, from_word(ni.x))); }
 };
 
-// forward radix-2^NB on 8>>NB independent groups held in v[]
-template <int NB, class A>
-__device__ __forceinline__ void fwd_radix(const A& ar, typename A::T (&v)[8], const typename A::TW* __restrict__ tw, const int (&twb)[8]) {
-    constexpr int G = 8 >> NB, R = 1 << NB;
+// forward radix-2^NB on EPT>>NB independent groups held in v[]
+template <int NB, int EPT, class A>
+__device__ __forceinline__ void fwd_radix(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
+    constexpr int G = EPT >> NB, R = 1 << NB;
 #pragma unroll
     for (int i = 0; i < NB; ++i) {
         const int half = 1 << (NB - 1 - i);
 #pragma unroll
         for (int g = 0; g < G; ++g) {
+            typename A::TW w[R / 2];
+            if (i == 0) w[0] = ar.ldtw(&tw[twb[g]]);
+            else {
+#pragma unroll
+                for (int m = 0; m < (1 << i); m += 2) ar.ldtw2(&tw[(twb[g] << i) + m], w[m], w[m + 1]);
+            }
 #pragma unroll
             for (int m = 0; m < (1 << i); ++m) {
-                const typename A::TW w = ar.ldtw(&tw[(twb[g] << i) + m]);
 #pragma unroll
                 for (int k0 = 0; k0 < half; ++k0) {
                     int a = g * R + m * 2 * half + k0;
-                    ar.ct(v[a], v[a + half], w);
+                    ar.ct(v[a], v[a + half], w[m]);
                 }
             }
         }
     }
 }
 // inverse radix-2^NB (bits ascending); twb[] is the twiddle index at the TOP bit of the round
-template <int NB, bool RECENTRE, class A>
-__device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[8], const typename A::TW* __restrict__ tw, const int (&twb)[8]) {
-    constexpr int G = 8 >> NB, R = 1 << NB;
+template <int NB, bool RECENTRE, int EPT, class A>
+__device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
+    constexpr int G = EPT >> NB, R = 1 << NB;
 #pragma unroll
     for (int i = 0; i < NB; ++i) {
         const int half = 1 << i;
 #pragma unroll
         for (int g = 0; g < G; ++g) {
+            typename A::TW w[R / 2];
+            if ((R >> (i + 1)) == 1) w[0] = ar.ldtw(&tw[twb[g] << (NB - 1 - i)]);
+            else {
+#pragma unroll
+                for (int m = 0; m < (R >> (i + 1)); m += 2) ar.ldtw2(&tw[(twb[g] << (NB - 1 - i)) + m], w[m], w[m + 1]);
+            }
 #pragma unroll
             for (int m = 0; m < (R >> (i + 1)); ++m) {
-                const typename A::TW w = ar.ldtw(&tw[(twb[g] << (NB - 1 - i)) + m]);
 #pragma unroll
                 for (int k0 = 0; k0 < half; ++k0) {
                     int a = g * R + m * 2 * half + k0;
-                    ar.gs(v[a], v[a + half], w);
+                    ar.gs(v[a], v[a + half], w[m]);
                 }
             }
         }
@@ -169,6 +187,7 @@ template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
 __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restrict__ src, u64* __restrict__ dst,
                                          const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN) {
     typedef typename A::T T;
+    constexpr int LOG_EPT = log_ept(STRIDED, FWD), EPT = 1 << LOG_EPT;
     constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
     const int tid = threadIdx.x;
     constexpr int logC = STRIDED ? LOG_E - nbits : 0;
@@ -180,13 +199,13 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
         return tile_base + li;
     };
 
-    constexpr int NR = (NBITS + 2) / 3, RBASE = NBITS / NR, REXTRA = NBITS % NR;
+    constexpr int NR = (NBITS + LOG_EPT - 1) / LOG_EPT, RBASE = NBITS / NR, REXTRA = NBITS % NR;
     const int row_stride = 1 << (logN - nbits);          // STRIDED: distance between consecutive tile rows in the limb
     int done = 0;
 #pragma unroll
     for (int r = 0; r < NR; ++r) {
         const int nb = RBASE + (r < REXTRA ? 1 : 0);
-        const int G = 8 >> nb;
+        const int G = EPT >> nb;
         const int pos = FWD ? lo_bit + nbits - done - nb : lo_bit + done;   // lowest bit of this round
         const int ptop = pos + nb - 1;
         // which register pairs sit in adjacent words (-> 128-bit global accesses): with pos == 0 elements e, e+1;
@@ -194,75 +213,75 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
         const int pair_step = pos == 0 ? 1 : (G >= 2 ? (1 << nb) : 0);
         // per group g: local index with the round's k bits zero, its shared-memory slot and its word index in the limb;
         // element (g, k) adds compile-time offsets to both
-        T v[8]; int sbase[8], gbase[8], twb[8];
+        T v[EPT]; int sbase[EPT], gbase[EPT], twb[EPT];
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
+        for (int g = 0; g < EPT; ++g) {
             if (g < G) {
                 const int base = insert_bits(tid * G + g, pos, nb, 0);
-                sbase[g] = pad(base);
+                sbase[g] = pad<LOG_EPT>(base);
                 gbase[g] = gidx(base);
             }
             twb[g] = (1 << (TOP - ptop)) + ((tid * G + g) >> pos) + (tile_base >> (ptop + 1));
         }
-        auto soff = [&](int e) { return sbase[e >> nb] + pad((e & ((1 << nb) - 1)) << pos); };
+        auto soff = [&](int e) { return sbase[e >> nb] + pad<LOG_EPT>((e & ((1 << nb) - 1)) << pos); };
         auto goff = [&](int e) {
             const int k = e & ((1 << nb) - 1);
             return gbase[e >> nb] + (STRIDED ? (k << (pos - logC)) * row_stride : (k << pos));
         };
         if (r == 0) {
-            u64 w[8];
+            u64 w[EPT];
             if (pair_step) {
 #pragma unroll
-                for (int e = 0; e < 8; ++e)
+                for (int e = 0; e < EPT; ++e)
                     if (!(e & pair_step)) {
                         const ulonglong2 t = *(const ulonglong2*)(src + goff(e));
                         w[e] = t.x; w[e + pair_step] = t.y;
                     }
             } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) w[e] = src[goff(e)];
+                for (int e = 0; e < EPT; ++e) w[e] = src[goff(e)];
             }
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = FINAL ? ar.from_raw(w[e]) : ar.from_word(w[e]);
+            for (int e = 0; e < EPT; ++e) v[e] = FINAL ? ar.from_raw(w[e]) : ar.from_word(w[e]);
         } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = ar.from_raw(sm[soff(e)]);
+            for (int e = 0; e < EPT; ++e) v[e] = ar.from_raw(sm[soff(e)]);
         }
         if (FWD) {
-            if (nb == 3) fwd_radix<3>(ar, v, tw, twb); else if (nb == 2) fwd_radix<2>(ar, v, tw, twb); else fwd_radix<1>(ar, v, tw, twb);
+            if (nb == 4) fwd_radix<(LOG_EPT >= 4 ? 4 : 3)>(ar, v, tw, twb); else if (nb == 3) fwd_radix<3, EPT>(ar, v, tw, twb); else if (nb == 2) fwd_radix<2, EPT>(ar, v, tw, twb); else fwd_radix<1, EPT>(ar, v, tw, twb);
         } else if (FINAL && r == NR - 1) {
-            if (nb == 3) inv_radix<3, false>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, false>(ar, v, tw, twb); else inv_radix<1, false>(ar, v, tw, twb);
+            if (nb == 4) inv_radix<(LOG_EPT >= 4 ? 4 : 3), false, EPT>(ar, v, tw, twb); else if (nb == 3) inv_radix<3, false, EPT>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, false, EPT>(ar, v, tw, twb); else inv_radix<1, false, EPT>(ar, v, tw, twb);
         } else {
-            if (nb == 3) inv_radix<3, true>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, true>(ar, v, tw, twb); else inv_radix<1, true>(ar, v, tw, twb);
+            if (nb == 4) inv_radix<(LOG_EPT >= 4 ? 4 : 3), true, EPT>(ar, v, tw, twb); else if (nb == 3) inv_radix<3, true, EPT>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, true, EPT>(ar, v, tw, twb); else inv_radix<1, true, EPT>(ar, v, tw, twb);
         }
         done += nb;
         if (r == NR - 1) {
-            u64 w[8];
+            u64 w[EPT];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
+            for (int e = 0; e < EPT; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
             if (pair_step) {
 #pragma unroll
-                for (int e = 0; e < 8; ++e)
+                for (int e = 0; e < EPT; ++e)
                     if (!(e & pair_step)) *(ulonglong2*)(dst + goff(e)) = make_ulonglong2(w[e], w[e + pair_step]);
             } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) dst[goff(e)] = w[e];
+                for (int e = 0; e < EPT; ++e) dst[goff(e)] = w[e];
             }
         } else {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) sm[soff(e)] = ar.to_raw(v[e]);
+            for (int e = 0; e < EPT; ++e) sm[soff(e)] = ar.to_raw(v[e]);
             __syncthreads();
         }
     }
 }
 
 template <int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
-__global__ void __launch_bounds__(1 << (LOG_E - 3))
+__global__ void __launch_bounds__(1 << (LOG_E - log_ept(STRIDED, FWD)))
 ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
          const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all,
          const ulonglong2* __restrict__ ninv_all, int logN) {
     OB_PDL_SYNC();
-    __shared__ __align__(16) u64 sm[(1 << LOG_E) + (1 << (LOG_E - 3))];      // padded layout, see pad()
+    __shared__ __align__(16) u64 sm[(1 << LOG_E) + (1 << (LOG_E - 3))];         // padded layout, see pad()
     const LimbDesc ld = limbs[blockIdx.y];
     const size_t N = (size_t)1 << logN;
     const ModConst& m = mc[ld.mod];
@@ -288,7 +307,7 @@ NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
 }
 
 #define OB_NTT_STRIDED(S1, FWD, FINAL, ...) \
-    OB_LAUNCH((ntt_pass<LOG_E_STRIDED, S1, true, FWD, FINAL>), g1, 1 << (LOG_E_STRIDED - 3), 0, stream(), __VA_ARGS__)
+    OB_LAUNCH((ntt_pass<LOG_E_STRIDED, S1, true, FWD, FINAL>), g1, 1 << (LOG_E_STRIDED - log_ept(true, FWD)), 0, stream(), __VA_ARGS__)
 #define OB_NTT_STRIDED_SWITCH(FWD, FINAL, ...) \
     switch (s1) { \
         case 4: OB_NTT_STRIDED(4, FWD, FINAL, __VA_ARGS__); break; \
@@ -305,7 +324,7 @@ void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p) {
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
     OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
-    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, true, true>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
+    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, true, true>), g2, 1 << (LOG_E_CONTIG - log_ept(false, true)), 0, stream(),
               (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
 }
 
@@ -313,7 +332,7 @@ void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
-    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, false, false>), g2, 1 << (LOG_E_CONTIG - 3), 0, stream(),
+    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, false, false>), g2, 1 << (LOG_E_CONTIG - log_ept(false, true)), 0, stream(),
               in, out, p.first, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN);
     OB_NTT_STRIDED_SWITCH(false, true, (const u64*)out, out, p.second, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN)
 }
