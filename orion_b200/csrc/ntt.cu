@@ -39,6 +39,14 @@ __host__ __device__ constexpr int log_ept(bool strided, bool fwd) { return (stri
 template <int LOG_EPT>
 __host__ __device__ constexpr int pad(int li) { return LOG_EPT == 4 ? li + (li >> 4) : li + (li >> 4) + ((li >> 5) << 1); }
 
+// 256-bit global accesses (sm_100: LDG/STG.E.ENL2.256): a lane moves a whole 32-byte sector
+__device__ __forceinline__ void ld_global_256(const u64* p, u64& a, u64& b, u64& c, u64& d) {
+    asm volatile("ld.global.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+}
+__device__ __forceinline__ void st_global_256(u64* p, u64 a, u64 b, u64 c, u64 d) {
+    asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(a), "l"(b), "l"(c), "l"(d) : "memory");
+}
+
 // ---- arithmetic policies ------------------------------------------------------------------------------------
 // ArithInt : Harvey lazy butterflies on u64 with Shoup twiddles (any prime < 2^62).  6 IMAD.WIDE + 4 IMAD per
 //            butterfly; IMAD.WIDE issues at 32 lanes/clk/SM on B200 (tools/ubench_int.cu), so this path tops out
@@ -228,9 +236,13 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
             const int k = e & ((1 << nb) - 1);
             return gbase[e >> nb] + (STRIDED ? (k << (pos - logC)) * row_stride : (k << pos));
         };
+        const bool quad = pos == 0 && nb >= 2;            // a thread owns runs of >= 4 adjacent words: 256-bit accesses
         if (r == 0) {
             u64 w[EPT];
-            if (pair_step) {
+            if (quad) {
+#pragma unroll
+                for (int e = 0; e < EPT; e += 4) ld_global_256(src + goff(e), w[e], w[e + 1], w[e + 2], w[e + 3]);
+            } else if (pair_step) {
 #pragma unroll
                 for (int e = 0; e < EPT; ++e)
                     if (!(e & pair_step)) {
@@ -259,7 +271,10 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
             u64 w[EPT];
 #pragma unroll
             for (int e = 0; e < EPT; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
-            if (pair_step) {
+            if (quad) {
+#pragma unroll
+                for (int e = 0; e < EPT; e += 4) st_global_256(dst + goff(e), w[e], w[e + 1], w[e + 2], w[e + 3]);
+            } else if (pair_step) {
 #pragma unroll
                 for (int e = 0; e < EPT; ++e)
                     if (!(e & pair_step)) *(ulonglong2*)(dst + goff(e)) = make_ulonglong2(w[e], w[e + pair_step]);
