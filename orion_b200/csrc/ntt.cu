@@ -73,7 +73,11 @@ struct ArithInt {
     __device__ __forceinline__ T from_raw(u64 x) const { return x; }           // inter-pass / shared-memory word
     __device__ __forceinline__ u64 to_raw(T x) const { return x; }
     __device__ __forceinline__ TW ldtw(const TW* p) const { return __ldg(p); }
-    __device__ __forceinline__ void ldtw2(const TW* p, TW& a, TW& b) const { a = __ldg(p); b = __ldg(p + 1); }
+    template <int CNT>
+    __device__ __forceinline__ void ldtwn(const TW* p, TW* w) const {
+#pragma unroll
+        for (int m = 0; m < CNT; ++m) w[m] = __ldg(p + m);
+    }
     __device__ __forceinline__ void ct(T& a, T& b, TW w) const {
         u64 x = a >= q2 ? a - q2 : a;                 // [0,2q)
         u64 v = shoup_lazy(b, w.x, w.y, q);           // [0,2q)
@@ -100,8 +104,21 @@ struct ArithF64 {
     __device__ __forceinline__ T from_raw(u64 x) const { return __longlong_as_double(x); }
     __device__ __forceinline__ u64 to_raw(T x) const { return (u64)__double_as_longlong(x); }
     __device__ __forceinline__ TW ldtw(const TW* p) const { return __ldg(p); }
-    // two consecutive twiddles (even index) as one 128-bit load: halves the sector requests of the late stages
-    __device__ __forceinline__ void ldtw2(const TW* p, TW& a, TW& b) const { const double2 t = __ldg((const double2*)p); a = t.x; b = t.y; }
+    // CNT consecutive twiddles starting at a CNT-aligned index: 256-bit / 128-bit loads, so a lane fetches whole sectors
+    template <int CNT>
+    __device__ __forceinline__ void ldtwn(const TW* p, TW* w) const {
+        if (CNT % 4 == 0) {
+#pragma unroll
+            for (int m = 0; m < CNT; m += 4)
+                asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(w[m]), "=d"(w[m + 1]), "=d"(w[m + 2]), "=d"(w[m + 3]) : "l"(p + m));
+        } else if (CNT % 2 == 0) {
+#pragma unroll
+            for (int m = 0; m < CNT; m += 2) { const double2 t = __ldg((const double2*)(p + m)); w[m] = t.x; w[m + 1] = t.y; }
+        } else {
+#pragma unroll
+            for (int m = 0; m < CNT; ++m) w[m] = __ldg(p + m);
+        }
+    }
     __device__ __forceinline__ T mulmod(T x, T w) const {                     // centred residue of x*w, |r| <= 0.7q
         const double h = __dmul_rn(x, w), l = __fma_rn(x, w, -h);
         const double t = __dsub_rn(__fma_rn(h, qinv, F64_MAGIC), F64_MAGIC);
@@ -127,57 +144,66 @@ struct ArithF64 {
     __device__ __forceinline__ u64 final_inv(T x, ulonglong2 ni) const { return to_word(mulmod(x, from_word(ni.x))); }
 };
 
-// forward radix-2^NB on EPT>>NB independent groups held in v[]
-template <int NB, int EPT, class A>
-__device__ __forceinline__ void fwd_radix(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
-    constexpr int G = EPT >> NB, R = 1 << NB;
+// One butterfly stage of a radix-2^NB round on EPT>>NB independent groups held in v[] (compile-time stage index I).
+// MERGED: the groups' twiddle indices are consecutive (rounds on the lowest index bits), so the stage's twiddles of ALL
+// groups are fetched as one aligned run (256-bit loads on the FP64 path).
+template <int NB, bool MERGED, int I, int EPT, class A>
+__device__ __forceinline__ void fwd_stage(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
+    if constexpr (I < NB) {
+        constexpr int G = EPT >> NB, R = 1 << NB, half = 1 << (NB - 1 - I), cnt = 1 << I;   // cnt twiddles per group
+        typename A::TW w[G * cnt];
+        if constexpr (MERGED) ar.template ldtwn<G * cnt>(&tw[twb[0] << I], w);
+        else {
 #pragma unroll
-    for (int i = 0; i < NB; ++i) {
-        const int half = 1 << (NB - 1 - i);
+            for (int g = 0; g < G; ++g) ar.template ldtwn<cnt>(&tw[twb[g] << I], w + g * cnt);
+        }
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-            typename A::TW w[R / 2];
-            if (i == 0) w[0] = ar.ldtw(&tw[twb[g]]);
-            else {
 #pragma unroll
-                for (int m = 0; m < (1 << i); m += 2) ar.ldtw2(&tw[(twb[g] << i) + m], w[m], w[m + 1]);
-            }
-#pragma unroll
-            for (int m = 0; m < (1 << i); ++m) {
+            for (int m = 0; m < cnt; ++m) {
 #pragma unroll
                 for (int k0 = 0; k0 < half; ++k0) {
-                    int a = g * R + m * 2 * half + k0;
-                    ar.ct(v[a], v[a + half], w[m]);
+                    const int a = g * R + m * 2 * half + k0;
+                    ar.ct(v[a], v[a + half], w[g * cnt + m]);
                 }
             }
         }
+        fwd_stage<NB, MERGED, I + 1>(ar, v, tw, twb);
     }
 }
-// inverse radix-2^NB (bits ascending); twb[] is the twiddle index at the TOP bit of the round
-template <int NB, bool RECENTRE, int EPT, class A>
-__device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
-    constexpr int G = EPT >> NB, R = 1 << NB;
+template <int NB, bool MERGED, int EPT, class A>
+__device__ __forceinline__ void fwd_radix(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
+    fwd_stage<NB, MERGED, 0>(ar, v, tw, twb);
+}
+// inverse (bits ascending); twb[] is the twiddle index at the TOP bit of the round
+template <int NB, bool MERGED, int I, int EPT, class A>
+__device__ __forceinline__ void inv_stage(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
+    if constexpr (I < NB) {
+        constexpr int G = EPT >> NB, R = 1 << NB, half = 1 << I, cnt = R >> (I + 1), sh = NB - 1 - I;
+        typename A::TW w[G * cnt];
+        if constexpr (MERGED) ar.template ldtwn<G * cnt>(&tw[twb[0] << sh], w);
+        else {
 #pragma unroll
-    for (int i = 0; i < NB; ++i) {
-        const int half = 1 << i;
+            for (int g = 0; g < G; ++g) ar.template ldtwn<cnt>(&tw[twb[g] << sh], w + g * cnt);
+        }
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-            typename A::TW w[R / 2];
-            if ((R >> (i + 1)) == 1) w[0] = ar.ldtw(&tw[twb[g] << (NB - 1 - i)]);
-            else {
 #pragma unroll
-                for (int m = 0; m < (R >> (i + 1)); m += 2) ar.ldtw2(&tw[(twb[g] << (NB - 1 - i)) + m], w[m], w[m + 1]);
-            }
-#pragma unroll
-            for (int m = 0; m < (R >> (i + 1)); ++m) {
+            for (int m = 0; m < cnt; ++m) {
 #pragma unroll
                 for (int k0 = 0; k0 < half; ++k0) {
-                    int a = g * R + m * 2 * half + k0;
-                    ar.gs(v[a], v[a + half], w[m]);
+                    const int a = g * R + m * 2 * half + k0;
+                    ar.gs(v[a], v[a + half], w[g * cnt + m]);
                 }
             }
         }
+        inv_stage<NB, MERGED, I + 1>(ar, v, tw, twb);
     }
+}
+template <int NB, bool RECENTRE, bool MERGED, int EPT, class A>
+__device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], const typename A::TW* __restrict__ tw, const int (&twb)[EPT]) {
+    constexpr int G = EPT >> NB, R = 1 << NB;
+    inv_stage<NB, MERGED, 0>(ar, v, tw, twb);
     if (RECENTRE) {      // only the sum outputs of the round's last stage can have grown (the others are fresh products)
 #pragma unroll
         for (int g = 0; g < G; ++g)
@@ -259,13 +285,16 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
 #pragma unroll
             for (int e = 0; e < EPT; ++e) v[e] = ar.from_raw(sm[soff(e)]);
         }
-        if (FWD) {
-            if (nb == 4) fwd_radix<(LOG_EPT >= 4 ? 4 : 3)>(ar, v, tw, twb); else if (nb == 3) fwd_radix<3, EPT>(ar, v, tw, twb); else if (nb == 2) fwd_radix<2, EPT>(ar, v, tw, twb); else fwd_radix<1, EPT>(ar, v, tw, twb);
-        } else if (FINAL && r == NR - 1) {
-            if (nb == 4) inv_radix<(LOG_EPT >= 4 ? 4 : 3), false, EPT>(ar, v, tw, twb); else if (nb == 3) inv_radix<3, false, EPT>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, false, EPT>(ar, v, tw, twb); else inv_radix<1, false, EPT>(ar, v, tw, twb);
-        } else {
-            if (nb == 4) inv_radix<(LOG_EPT >= 4 ? 4 : 3), true, EPT>(ar, v, tw, twb); else if (nb == 3) inv_radix<3, true, EPT>(ar, v, tw, twb); else if (nb == 2) inv_radix<2, true, EPT>(ar, v, tw, twb); else inv_radix<1, true, EPT>(ar, v, tw, twb);
-        }
+        const bool merged = pos == 0;                     // consecutive groups -> consecutive twiddle indices
+#define OB_RADIX(FN, ...) do { \
+        if (nb == 4) { if (merged) FN<(LOG_EPT >= 4 ? 4 : 3), __VA_ARGS__ true, EPT>(ar, v, tw, twb); else FN<(LOG_EPT >= 4 ? 4 : 3), __VA_ARGS__ false, EPT>(ar, v, tw, twb); } \
+        else if (nb == 3) { if (merged) FN<3, __VA_ARGS__ true, EPT>(ar, v, tw, twb); else FN<3, __VA_ARGS__ false, EPT>(ar, v, tw, twb); } \
+        else if (nb == 2) { if (merged) FN<2, __VA_ARGS__ true, EPT>(ar, v, tw, twb); else FN<2, __VA_ARGS__ false, EPT>(ar, v, tw, twb); } \
+        else { if (merged) FN<1, __VA_ARGS__ true, EPT>(ar, v, tw, twb); else FN<1, __VA_ARGS__ false, EPT>(ar, v, tw, twb); } } while (0)
+        if (FWD) OB_RADIX(fwd_radix, );
+        else if (FINAL && r == NR - 1) OB_RADIX(inv_radix, false, );
+        else OB_RADIX(inv_radix, true, );
+#undef OB_RADIX
         done += nb;
         if (r == NR - 1) {
             u64 w[EPT];
