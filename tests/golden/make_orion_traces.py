@@ -288,6 +288,10 @@ def build_model(name):
         net = models.LoLA()
         x = (torch.rand(1, 1, 28, 28) - 0.1307) / 0.3081
         cfg = os.path.join(REF, "configs", "lola2.yml")
+    elif name == "mlp_ci":                                   # the reference's own test config: tests/configs/mlp.yml
+        net = models.MLP()
+        x = (torch.rand(1, 1, 28, 28) - 0.1307) / 0.3081
+        cfg = os.path.join(REF, "tests", "configs", "mlp.yml")
     elif name == "lola_ci":                                  # configs/lola.yml as shipped: ConjugateInvariant ring, logN=13
         net = models.LoLA()
         x = (torch.rand(1, 1, 28, 28) - 0.1307) / 0.3081
@@ -317,7 +321,7 @@ def main():
     cfg = yaml.safe_load(open(cfg_path))
     cfg["orion"]["debug"] = False
     cfg["orion"]["io_mode"] = "none"                       # run with TORCHDYNAMO_DISABLE=1 where inductor cannot compile
-    if name != "lola_ci":
+    if name not in ("lola_ci", "mlp_ci"):
         cfg["ckks_params"]["RingType"] = "standard"
     for a in sys.argv[2:]:
         if a.startswith("--logn="):
