@@ -257,11 +257,13 @@ def main():
     # boot LogP 8x61; 147 linear transforms, 138 polynomial evaluations, 28 bootstraps), recorded from the unmodified
     # reference and replayed through the drop-in boundary; every rank runs its own image (image-sharded, no collective).
     resnet = None
+    lola = None
     if not args.no_resnet:
         for d in [dev_in, dev_out] + big + evks:
             lib.B200_DevFree(d)
         ctx.close()
         resnet = run_resnet(lib, rank, world, dist if world > 1 else None, torch)
+        lola = run_lola(lib, rank, world, dist if world > 1 else None, torch)
 
     if rank == 0:
         cpu = None
@@ -291,16 +293,19 @@ def main():
             line["cpu_baseline"] = cpu
         if resnet:
             line["resnet20"] = resnet
+        if lola:
+            line["lola2"] = lola
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_resnet(lib, rank, world, dist, torch, reps=3):
+def run_trace_timed(name, lib, rank, world, dist, torch, reps=3):
+    """Replay the reference's recorded call trace `name`, one image per rank; returns timing fields or None."""
     from orion_b200.bindings import B200Library
     from orion_b200.replay import Replayer, Trace
     gold = os.path.join(ROOT, "tests", "golden")
-    jp, npz = os.path.join(gold, "trace_resnet20.json"), os.path.join(gold, "trace_resnet20.npz")
+    jp, npz = os.path.join(gold, "trace_%s.json" % name), os.path.join(gold, "trace_%s.npz" % name)
     if not os.path.exists(jp):
         return None
     B = B200Library()
@@ -327,10 +332,29 @@ def run_resnet(lib, rank, world, dist, torch, reps=3):
         sec = float(tt.item())
     B.DeleteScheme()
     return {"s_per_image": sec, "images_per_s": world / sec, "n_gpus": world, "setup_s": setup_s,
-            "launches_per_image": int(launches), "bootstraps": 28, "linear_transforms": 147, "poly_evals": 138,
+            "launches_per_image": int(launches), "counts": {k: r.counts.get(k, 0) // (reps + 2) for k in
+                                                           ("EvaluateLinearTransform", "EvaluatePolynomial", "Bootstrap", "MulRelinCiphertextNew")}}
+
+
+def run_resnet(lib, rank, world, dist, torch, reps=3):
+    res = run_trace_timed("resnet20", lib, rank, world, dist, torch, reps)
+    if res is None:
+        return None
+    res.update({"bootstraps": 28, "linear_transforms": 147, "poly_evals": 138,
             "config": "configs/resnet.yml as shipped (logN=13, LogQ 60+32x30, LogP 60x2, boot LogP 61x8), one image per GPU",
             "data": "synthetic payloads of the recorded shapes (call trace of the unmodified reference)",
-            "e2e": "includes encode+encrypt (H2D) of the image and decrypt+decode (D2H) of the logits"}
+            "e2e": "includes encode+encrypt (H2D) of the image and decrypt+decode (D2H) of the logits"})
+    return res
+
+
+def run_lola(lib, rank, world, dist, torch):
+    """BASELINE configs[2]: LoLA with configs/lola2.yml (logN=14, 7+2 limbs), independent images sharded over the ranks."""
+    res = run_trace_timed("lola", lib, rank, world, dist, torch, reps=5)
+    if res is None:
+        return None
+    res.update({"config": "configs/lola2.yml (logN=14, LogQ 60+6x30, LogP 60x2), one image per GPU per pass",
+                "data": "synthetic MNIST-shaped image, full recorded payloads (call trace of the unmodified reference)"})
+    return res
 
 
 def ctypes_cast(ptr, words):
