@@ -202,31 +202,43 @@ inner_product_multi_kernel(const u64* __restrict__ c1, size_t c1_zstride, const 
                            const ulonglong2* __restrict__ pmodq, const ModConst* __restrict__ mc) {
     OB_PDL_SYNC();
     const int t = blockIdx.y, z = blockIdx.z, W = L + K;
-    const int x = blockIdx.x * TPB + threadIdx.x;
+    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;          // two adjacent coefficients per thread: 128-bit streams
     const int ci = t < L ? t : nQ + (t - L);
     const ModConst mm = mc[ci];
     const int own = t < L ? t / K : -1;
     const u64* __restrict__ evk = m.evk[z];
     const u64* __restrict__ c1z = c1 + (size_t)z * c1_zstride;
     const u64* __restrict__ dz = digits + (size_t)z * dig_zstride;
-    u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
+    u64 h0a = 0, l0a = 0, h1a = 0, l1a = 0, h0b = 0, l0b = 0, h1b = 0, l1b = 0;
+#pragma unroll 2
     for (int j = 0; j < beta; ++j) {
-        const u64 d = (j == own) ? c1z[(size_t)t * N + x] : dz[((size_t)j * W + t) * N + x];
-        const u64 k0 = evk[(((size_t)j * 2 + 0) * nmod + ci) * N + x];
-        const u64 k1 = evk[(((size_t)j * 2 + 1) * nmod + ci) * N + x];
-        mac128(h0, l0, d, k0, mm.q);
-        mac128(h1, l1, d, k1, mm.q);
+        const ulonglong2 d = *(const ulonglong2*)((j == own) ? c1z + (size_t)t * N + x : dz + ((size_t)j * W + t) * N + x);
+        const ulonglong2 k0 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 0) * nmod + ci) * N + x);
+        const ulonglong2 k1 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 1) * nmod + ci) * N + x);
+        mac128(h0a, l0a, d.x, k0.x, mm.q); mac128(h0b, l0b, d.y, k0.y, mm.q);
+        mac128(h1a, l1a, d.x, k1.x, mm.q); mac128(h1b, l1b, d.y, k1.y, mm.q);
     }
-    u64 r0 = mont_redc(h0, l0, mm.q, mm.qinv_neg), r1 = mont_redc(h1, l1, mm.q, mm.qinv_neg);
+    ulonglong2 r0 = make_ulonglong2(mont_redc(h0a, l0a, mm.q, mm.qinv_neg), mont_redc(h0b, l0b, mm.q, mm.qinv_neg));
+    ulonglong2 r1 = make_ulonglong2(mont_redc(h1a, l1a, mm.q, mm.qinv_neg), mont_redc(h1b, l1b, mm.q, mm.qinv_neg));
     if (ADD_MODE == 1) {
-        if (t < L) { const ulonglong2 w = pmodq[t]; r0 = add_mod(r0, shoup_mul(addend[(size_t)z * addend_zstride + (size_t)t * N + x], w.x, w.y, mm.q), mm.q); }
+        if (t < L) {
+            const ulonglong2 w = pmodq[t];
+            const ulonglong2 e = *(const ulonglong2*)(addend + (size_t)z * addend_zstride + (size_t)t * N + x);
+            r0.x = add_mod(r0.x, shoup_mul(e.x, w.x, w.y, mm.q), mm.q); r0.y = add_mod(r0.y, shoup_mul(e.y, w.x, w.y, mm.q), mm.q);
+        }
     } else if (ADD_MODE == 2) {
-        r0 = add_mod(r0, addend[(size_t)z * addend_zstride + (size_t)t * N + x], mm.q);
+        const ulonglong2 e = *(const ulonglong2*)(addend + (size_t)z * addend_zstride + (size_t)t * N + x);
+        r0.x = add_mod(r0.x, e.x, mm.q); r0.y = add_mod(r0.y, e.y, mm.q);
     }
     const uint32_t* __restrict__ sc = m.scatter[z];
-    const int xo = sc ? (int)__ldg(&sc[x]) : x;
     u64* o = out + (size_t)z * out_zstride;
-    o[(size_t)t * N + xo] = r0; o[((size_t)W + t) * N + xo] = r1;
+    if (sc) {
+        const uint2 xo = __ldg((const uint2*)(sc + x));
+        o[(size_t)t * N + xo.x] = r0.x; o[(size_t)t * N + xo.y] = r0.y;
+        o[((size_t)W + t) * N + xo.x] = r1.x; o[((size_t)W + t) * N + xo.y] = r1.y;
+    } else {
+        *(ulonglong2*)(o + (size_t)t * N + x) = r0; *(ulonglong2*)(o + ((size_t)W + t) * N + x) = r1;
+    }
 }
 
 // out[p][t][x] = sum_z in[z][p][t][x]  (mod q_t), QP layout with W limbs per polynomial
@@ -375,7 +387,7 @@ void ks_inner_product_multi(Context& c, int level, int n, const u64* c1, size_t 
                             const IpMulti& m, u64* out, size_t out_zstride, int add_mode, const u64* addend, size_t addend_zstride) {
     OB_CHECK(n >= 1 && n <= IPM_MAX, "inner product batch size");
     const int L = level + 1, K = c.nP, W = L + K, beta = c.num_digits(level);
-    dim3 grid(c.N / TPB, W, n);
+    dim3 grid(c.N / (2 * TPB), W, n);
 #define OB_IPM(MODE) OB_LAUNCH((inner_product_multi_kernel<MODE>), grid, TPB, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out, \
                                out_zstride, addend, addend_zstride, c.N, L, K, c.nQ, c.nmod, beta, c.d_pmodq.as<ulonglong2>(), c.dmc())
     if (add_mode == 1) OB_IPM(1); else if (add_mode == 2) OB_IPM(2); else OB_IPM(0);
