@@ -107,56 +107,67 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
         s_sq[i] = m.q; s_sqd[i] = m.qd; s_inv[i] = d.inv[i]; s_sh[i] = CENTERED ? d.half_src[i] : 0;
     }
     __syncthreads();
-    const int x = blockIdx.x * BC_TPB + threadIdx.x;
-    u64 y[NS];
-    double yd[NS];
-    double vf = 0.0;
+    // two adjacent coefficients per thread: 128-bit loads/stores, and the per-destination constants (matrix column,
+    // modulus, correction row) are fetched from shared memory once for both
+    const int x = (blockIdx.x * BC_TPB + threadIdx.x) * 2;
+    u64 y[2][NS];
+    double yd[2][NS];
+    double vf0 = 0.0, vf1 = 0.0;
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
         if (i < ns) {
             const u64 q = s_sq[i];
-            u64 xi = in[(size_t)(d.in_off + i) * N + x];
-            if (CENTERED) xi = add_mod(xi, s_sh[i], q);
+            ulonglong2 xi = *(const ulonglong2*)(in + (size_t)(d.in_off + i) * N + x);
+            if (CENTERED) { xi.x = add_mod(xi.x, s_sh[i], q); xi.y = add_mod(xi.y, s_sh[i], q); }
             const ulonglong2 w = s_inv[i];
-            y[i] = shoup_mul(xi, w.x, w.y, q);
-            yd[i] = __ull2double_rn(y[i]);             // exact below 2^53
-            vf = __dadd_rn(vf, __ddiv_rn(yd[i], s_sqd[i]));
+            y[0][i] = shoup_mul(xi.x, w.x, w.y, q); y[1][i] = shoup_mul(xi.y, w.x, w.y, q);
+            yd[0][i] = __ull2double_rn(y[0][i]); yd[1][i] = __ull2double_rn(y[1][i]);      // exact below 2^53
+            const double qd = s_sqd[i];
+            vf0 = __dadd_rn(vf0, __ddiv_rn(yd[0][i], qd)); vf1 = __dadd_rn(vf1, __ddiv_rn(yd[1][i], qd));
         }
     }
-    const u64 v = (ns == 1 && !CENTERED) ? 0 : (u64)vf;
+    const u64 v0 = (ns == 1 && !CENTERED) ? 0 : (u64)vf0, v1 = (ns == 1 && !CENTERED) ? 0 : (u64)vf1;
 #pragma unroll 2
     for (int t = 0; t < nd; ++t) {
         const u64 q = s_dq[t];
         const double qinv = s_dqinv[t];
-        u64 r;
+        ulonglong2 r;
         if (!CENTERED && qinv != 0.0) {
             // FP64 contraction (sources and destination of at most 46 bits): each product is reduced to a centred
             // residue with 6 exact DFMA-class operations; B200 issues those at twice the rate of IMAD.WIDE
             const double qd = __ull2double_rn(q);
             const double M = 6755399441055744.0;
-            double acc = s_negd[t * (ns + 1) + v];
+            double a0 = s_negd[t * (ns + 1) + v0], a1 = s_negd[t * (ns + 1) + v1];
 #pragma unroll
             for (int i = 0; i < NS; ++i)
                 if (i < ns) {
                     const double w = s_matd[i * nd + t];
-                    const double h = __dmul_rn(yd[i], w), l = __fma_rn(yd[i], w, -h);
-                    const double tq = __dsub_rn(__fma_rn(h, qinv, M), M);
-                    acc = __dadd_rn(acc, __dadd_rn(__fma_rn(-tq, qd, h), l));
+                    const double h0 = __dmul_rn(yd[0][i], w), l0 = __fma_rn(yd[0][i], w, -h0);
+                    const double h1 = __dmul_rn(yd[1][i], w), l1 = __fma_rn(yd[1][i], w, -h1);
+                    const double t0 = __dsub_rn(__fma_rn(h0, qinv, M), M), t1 = __dsub_rn(__fma_rn(h1, qinv, M), M);
+                    a0 = __dadd_rn(a0, __dadd_rn(__fma_rn(-t0, qd, h0), l0));
+                    a1 = __dadd_rn(a1, __dadd_rn(__fma_rn(-t1, qd, h1), l1));
                 }
-            const double tq = __dsub_rn(__fma_rn(acc, qinv, M), M);
-            acc = __fma_rn(-tq, qd, acc);
-            acc = acc < 0.0 ? __dadd_rn(acc, qd) : acc;
-            r = (u64)__double_as_longlong(__dadd_rn(acc, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+            const double t0 = __dsub_rn(__fma_rn(a0, qinv, M), M), t1 = __dsub_rn(__fma_rn(a1, qinv, M), M);
+            a0 = __fma_rn(-t0, qd, a0); a1 = __fma_rn(-t1, qd, a1);
+            a0 = a0 < 0.0 ? __dadd_rn(a0, qd) : a0; a1 = a1 < 0.0 ? __dadd_rn(a1, qd) : a1;
+            r.x = (u64)__double_as_longlong(__dadd_rn(a0, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+            r.y = (u64)__double_as_longlong(__dadd_rn(a1, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
         } else {
-            u64 hi = 0, lo = 0;
+            u64 hi0 = 0, lo0 = 0, hi1 = 0, lo1 = 0;
 #pragma unroll
             for (int i = 0; i < NS; ++i)
-                if (i < ns) { if (NS <= 3) mac128_raw(hi, lo, y[i], s_mat[i * nd + t]); else mac128(hi, lo, y[i], s_mat[i * nd + t], q); }
-            r = mont_redc(hi, lo, q, s_dqi[t]);
-            r = add_mod(r, s_neg[t * (ns + 1) + v], q);
-            if (CENTERED) r = sub_mod(r, s_dh[t], q);
+                if (i < ns) {
+                    const u64 w = s_mat[i * nd + t];
+                    if (NS <= 3) { mac128_raw(hi0, lo0, y[0][i], w); mac128_raw(hi1, lo1, y[1][i], w); }
+                    else { mac128(hi0, lo0, y[0][i], w, q); mac128(hi1, lo1, y[1][i], w, q); }
+                }
+            const u64 qi = s_dqi[t];
+            r.x = add_mod(mont_redc(hi0, lo0, q, qi), s_neg[t * (ns + 1) + v0], q);
+            r.y = add_mod(mont_redc(hi1, lo1, q, qi), s_neg[t * (ns + 1) + v1], q);
+            if (CENTERED) { const u64 h = s_dh[t]; r.x = sub_mod(r.x, h, q); r.y = sub_mod(r.y, h, q); }
         }
-        out[(size_t)s_off[t] * N + x] = r;
+        *(ulonglong2*)(out + (size_t)s_off[t] * N + x) = r;
     }
 }
 
@@ -364,7 +375,7 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered) {
     if (b.n == 0) return;
     OB_CHECK(b.smem <= 48 * 1024, "base conversion tables exceed the static shared-memory window");
-    dim3 grid(c.N / BC_TPB, b.n);
+    dim3 grid(c.N / (2 * BC_TPB), b.n);
 #define OB_BC(NSV) do { if (centered) OB_LAUNCH((baseconv_batch_kernel<true, NSV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); \
                        else OB_LAUNCH((baseconv_batch_kernel<false, NSV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
     if (b.max_ns <= 1) OB_BC(1); else if (b.max_ns <= 2) OB_BC(2); else if (b.max_ns <= 3) OB_BC(3); else if (b.max_ns <= 4) OB_BC(4);
