@@ -72,7 +72,11 @@ __device__ __forceinline__ void mac128_raw(u64& hi, u64& lo, u64 a, u64 b) {
     lo += pl;
     hi += ph + (lo < pl);
 }
-template <bool CENTERED, int NS>      // NS = compile-time bound on the source-limb count of every conversion in the batch
+// NS = compile-time bound on the source-limb count of every conversion in the batch.  VEC = adjacent coefficients per
+// thread (2: 128-bit loads/stores and every per-destination constant fetched once for both -- large rings; 1: twice
+// the threads -- small rings).  gridDim.z splits the destination limbs into chunks so that a conversion of a small
+// ring (logN = 13, 8 x 61-bit special primes in the bootstrapping chain) still fills the 148 SMs.
+template <bool CENTERED, int NS, int VEC>
 __global__ void __launch_bounds__(BC_TPB)
 baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                       const ModConst* __restrict__ mc) {
@@ -80,94 +84,123 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const BcDev d = descs[blockIdx.y];
     const int ns = d.ns, nd = d.nd;
-    u64* s_mat = (u64*)smem_raw;                       // [ns][nd]
-    u64* s_neg = s_mat + ns * nd;                      // [nd][ns+1]
-    double* s_matd = (double*)(s_neg + nd * (ns + 1)); // [ns][nd]
-    double* s_negd = s_matd + ns * nd;                 // [nd][ns+1]
-    u64* s_dq = (u64*)(s_negd + nd * (ns + 1));        // [nd]
-    u64* s_dqi = s_dq + nd;                            // [nd]
-    u64* s_dh = s_dqi + nd;                            // [nd]
-    double* s_dqinv = (double*)(s_dh + nd);            // [nd]  1/q as double; 0 marks an integer-path destination
-    u64* s_sq = (u64*)(s_dqinv + nd);                  // [ns]
+    const int chunk = (nd + gridDim.z - 1) / gridDim.z;
+    const int t0 = blockIdx.z * chunk, ndc = min(nd, t0 + chunk) - t0;          // this CTA's destinations [t0, t0+ndc)
+    if (ndc <= 0) return;
+    u64* s_mat = (u64*)smem_raw;                       // [ns][chunk]
+    u64* s_neg = s_mat + ns * chunk;                   // [chunk][ns+1]
+    double* s_matd = (double*)(s_neg + chunk * (ns + 1)); // [ns][chunk]
+    double* s_negd = s_matd + ns * chunk;              // [chunk][ns+1]
+    u64* s_dq = (u64*)(s_negd + chunk * (ns + 1));     // [chunk]
+    u64* s_dqi = s_dq + chunk;                         // [chunk]
+    u64* s_dh = s_dqi + chunk;                         // [chunk]
+    double* s_dqinv = (double*)(s_dh + chunk);         // [chunk]  1/q as double; 0 marks an integer-path destination
+    u64* s_sq = (u64*)(s_dqinv + chunk);               // [ns]
     u64* s_sh = s_sq + ns;                             // [ns]
     double* s_sqd = (double*)(s_sh + ns);              // [ns]
     ulonglong2* s_inv = (ulonglong2*)(s_sqd + ns + (ns & 1));   // [ns], 16-byte aligned
-    int* s_off = (int*)(s_inv + ns);                   // [nd]
+    int* s_off = (int*)(s_inv + ns);                   // [chunk]
     const bool f64 = !CENTERED && d.f64_src;
-    for (int i = threadIdx.x; i < ns * nd; i += BC_TPB) { s_mat[i] = d.mat[i]; s_matd[i] = d.mat_d[i]; }
-    for (int i = threadIdx.x; i < nd * (ns + 1); i += BC_TPB) { s_neg[i] = d.negvq[i]; s_negd[i] = d.negvq_d[i]; }
-    for (int i = threadIdx.x; i < nd; i += BC_TPB) {
-        const ModConst& m = mc[d.dst_mod[i]];
-        s_dq[i] = m.q; s_dqi[i] = m.qinv_neg; s_dh[i] = CENTERED ? d.half_dst[i] : 0;
+    for (int i = threadIdx.x; i < ns * ndc; i += BC_TPB) {
+        const int r = i / ndc, t = i - r * ndc;
+        s_mat[r * chunk + t] = d.mat[r * nd + t0 + t]; s_matd[r * chunk + t] = d.mat_d[r * nd + t0 + t];
+    }
+    for (int i = threadIdx.x; i < ndc * (ns + 1); i += BC_TPB) {
+        s_neg[i] = d.negvq[t0 * (ns + 1) + i]; s_negd[i] = d.negvq_d[t0 * (ns + 1) + i];
+    }
+    for (int i = threadIdx.x; i < ndc; i += BC_TPB) {
+        const ModConst& m = mc[d.dst_mod[t0 + i]];
+        s_dq[i] = m.q; s_dqi[i] = m.qinv_neg; s_dh[i] = CENTERED ? d.half_dst[t0 + i] : 0;
         s_dqinv[i] = (f64 && m.bits <= BC_F64_BITS) ? m.qinv_d : 0.0;
-        s_off[i] = d.out_base + (int)d.out_off[i].in_off;
+        s_off[i] = d.out_base + (int)d.out_off[t0 + i].in_off;
     }
     for (int i = threadIdx.x; i < ns; i += BC_TPB) {
         const ModConst& m = mc[d.src_mod[i]];
         s_sq[i] = m.q; s_sqd[i] = m.qd; s_inv[i] = d.inv[i]; s_sh[i] = CENTERED ? d.half_src[i] : 0;
     }
     __syncthreads();
-    // two adjacent coefficients per thread: 128-bit loads/stores, and the per-destination constants (matrix column,
-    // modulus, correction row) are fetched from shared memory once for both
-    const int x = (blockIdx.x * BC_TPB + threadIdx.x) * 2;
-    u64 y[2][NS];
-    double yd[2][NS];
-    double vf0 = 0.0, vf1 = 0.0;
+    const int x = (blockIdx.x * BC_TPB + threadIdx.x) * VEC;
+    u64 y[VEC][NS];
+    double yd[VEC][NS];
+    double vf[VEC];
+#pragma unroll
+    for (int c = 0; c < VEC; ++c) vf[c] = 0.0;
 #pragma unroll
     for (int i = 0; i < NS; ++i) {
         if (i < ns) {
             const u64 q = s_sq[i];
-            ulonglong2 xi = *(const ulonglong2*)(in + (size_t)(d.in_off + i) * N + x);
-            if (CENTERED) { xi.x = add_mod(xi.x, s_sh[i], q); xi.y = add_mod(xi.y, s_sh[i], q); }
+            u64 xi[VEC];
+            const u64* src = in + (size_t)(d.in_off + i) * N + x;
+            if (VEC == 2) { const ulonglong2 t = *(const ulonglong2*)src; xi[0] = t.x; xi[VEC - 1] = t.y; }
+            else xi[0] = *src;
             const ulonglong2 w = s_inv[i];
-            y[0][i] = shoup_mul(xi.x, w.x, w.y, q); y[1][i] = shoup_mul(xi.y, w.x, w.y, q);
-            yd[0][i] = __ull2double_rn(y[0][i]); yd[1][i] = __ull2double_rn(y[1][i]);      // exact below 2^53
             const double qd = s_sqd[i];
-            vf0 = __dadd_rn(vf0, __ddiv_rn(yd[0][i], qd)); vf1 = __dadd_rn(vf1, __ddiv_rn(yd[1][i], qd));
+#pragma unroll
+            for (int c = 0; c < VEC; ++c) {
+                if (CENTERED) xi[c] = add_mod(xi[c], s_sh[i], q);
+                y[c][i] = shoup_mul(xi[c], w.x, w.y, q);
+                yd[c][i] = __ull2double_rn(y[c][i]);                      // exact below 2^53
+                vf[c] = __dadd_rn(vf[c], __ddiv_rn(yd[c][i], qd));
+            }
         }
     }
-    const u64 v0 = (ns == 1 && !CENTERED) ? 0 : (u64)vf0, v1 = (ns == 1 && !CENTERED) ? 0 : (u64)vf1;
+    // a single source modulus without centring is a plain copy + reduction (v is 0 by definition)
+    int v[VEC];
+#pragma unroll
+    for (int c = 0; c < VEC; ++c) v[c] = (ns == 1 && !CENTERED) ? 0 : (int)vf[c];
 #pragma unroll 2
-    for (int t = 0; t < nd; ++t) {
+    for (int t = 0; t < ndc; ++t) {
         const u64 q = s_dq[t];
         const double qinv = s_dqinv[t];
-        ulonglong2 r;
+        u64 r[VEC];
         if (!CENTERED && qinv != 0.0) {
             // FP64 contraction (sources and destination of at most 46 bits): each product is reduced to a centred
             // residue with 6 exact DFMA-class operations; B200 issues those at twice the rate of IMAD.WIDE
             const double qd = __ull2double_rn(q);
             const double M = 6755399441055744.0;
-            double a0 = s_negd[t * (ns + 1) + v0], a1 = s_negd[t * (ns + 1) + v1];
+            double a[VEC];
+#pragma unroll
+            for (int c = 0; c < VEC; ++c) a[c] = s_negd[t * (ns + 1) + v[c]];
 #pragma unroll
             for (int i = 0; i < NS; ++i)
                 if (i < ns) {
-                    const double w = s_matd[i * nd + t];
-                    const double h0 = __dmul_rn(yd[0][i], w), l0 = __fma_rn(yd[0][i], w, -h0);
-                    const double h1 = __dmul_rn(yd[1][i], w), l1 = __fma_rn(yd[1][i], w, -h1);
-                    const double t0 = __dsub_rn(__fma_rn(h0, qinv, M), M), t1 = __dsub_rn(__fma_rn(h1, qinv, M), M);
-                    a0 = __dadd_rn(a0, __dadd_rn(__fma_rn(-t0, qd, h0), l0));
-                    a1 = __dadd_rn(a1, __dadd_rn(__fma_rn(-t1, qd, h1), l1));
+                    const double w = s_matd[i * chunk + t];
+#pragma unroll
+                    for (int c = 0; c < VEC; ++c) {
+                        const double h = __dmul_rn(yd[c][i], w), l = __fma_rn(yd[c][i], w, -h);
+                        const double tq = __dsub_rn(__fma_rn(h, qinv, M), M);
+                        a[c] = __dadd_rn(a[c], __dadd_rn(__fma_rn(-tq, qd, h), l));
+                    }
                 }
-            const double t0 = __dsub_rn(__fma_rn(a0, qinv, M), M), t1 = __dsub_rn(__fma_rn(a1, qinv, M), M);
-            a0 = __fma_rn(-t0, qd, a0); a1 = __fma_rn(-t1, qd, a1);
-            a0 = a0 < 0.0 ? __dadd_rn(a0, qd) : a0; a1 = a1 < 0.0 ? __dadd_rn(a1, qd) : a1;
-            r.x = (u64)__double_as_longlong(__dadd_rn(a0, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
-            r.y = (u64)__double_as_longlong(__dadd_rn(a1, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+#pragma unroll
+            for (int c = 0; c < VEC; ++c) {
+                const double tq = __dsub_rn(__fma_rn(a[c], qinv, M), M);
+                double ac = __fma_rn(-tq, qd, a[c]);
+                ac = ac < 0.0 ? __dadd_rn(ac, qd) : ac;
+                r[c] = (u64)__double_as_longlong(__dadd_rn(ac, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+            }
         } else {
-            u64 hi0 = 0, lo0 = 0, hi1 = 0, lo1 = 0;
+            u64 hi[VEC], lo[VEC];
+#pragma unroll
+            for (int c = 0; c < VEC; ++c) hi[c] = lo[c] = 0;
 #pragma unroll
             for (int i = 0; i < NS; ++i)
                 if (i < ns) {
-                    const u64 w = s_mat[i * nd + t];
-                    if (NS <= 3) { mac128_raw(hi0, lo0, y[0][i], w); mac128_raw(hi1, lo1, y[1][i], w); }
-                    else { mac128(hi0, lo0, y[0][i], w, q); mac128(hi1, lo1, y[1][i], w, q); }
+                    const u64 w = s_mat[i * chunk + t];
+#pragma unroll
+                    for (int c = 0; c < VEC; ++c) {
+                        if (NS <= 3) mac128_raw(hi[c], lo[c], y[c][i], w); else mac128(hi[c], lo[c], y[c][i], w, q);
+                    }
                 }
             const u64 qi = s_dqi[t];
-            r.x = add_mod(mont_redc(hi0, lo0, q, qi), s_neg[t * (ns + 1) + v0], q);
-            r.y = add_mod(mont_redc(hi1, lo1, q, qi), s_neg[t * (ns + 1) + v1], q);
-            if (CENTERED) { const u64 h = s_dh[t]; r.x = sub_mod(r.x, h, q); r.y = sub_mod(r.y, h, q); }
+#pragma unroll
+            for (int c = 0; c < VEC; ++c) {
+                r[c] = add_mod(mont_redc(hi[c], lo[c], q, qi), s_neg[t * (ns + 1) + v[c]], q);
+                if (CENTERED) r[c] = sub_mod(r[c], s_dh[t], q);
+            }
         }
-        *(ulonglong2*)(out + (size_t)s_off[t] * N + x) = r;
+        u64* dst = out + (size_t)s_off[t] * N + x;
+        if (VEC == 2) *(ulonglong2*)dst = make_ulonglong2(r[0], r[VEC - 1]); else *dst = r[0];
     }
 }
 
@@ -363,6 +396,7 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
         const size_t sm = 8 * (2 * (ns * nd + nd * (ns + 1)) + 4 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 8 * nd + 16;
         b.smem = std::max(b.smem, sm);
         b.max_ns = std::max(b.max_ns, bc.ns);
+        b.min_nd = std::min(b.min_nd, bc.nd);
     }
     auto buf = std::make_unique<DevBuf>(h.size() * sizeof(BcDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, h.data(), h.size() * sizeof(BcDev), cudaMemcpyHostToDevice, stream()));
@@ -375,11 +409,19 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered) {
     if (b.n == 0) return;
     OB_CHECK(b.smem <= 48 * 1024, "base conversion tables exceed the static shared-memory window");
-    dim3 grid(c.N / (2 * BC_TPB), b.n);
-#define OB_BC(NSV) do { if (centered) OB_LAUNCH((baseconv_batch_kernel<true, NSV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); \
-                       else OB_LAUNCH((baseconv_batch_kernel<false, NSV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+    // size the launch for >= ~2 CTAs of work per SM: one coefficient per thread and the destination limbs split over
+    // gridDim.z when the ring is small, two coefficients per thread and no split when it is large
+    const long want = 148L * 2048;
+    const int vec = ((long)c.N / 2) * b.n >= want ? 2 : 1;
+    const long thr = ((long)c.N / vec) * b.n;
+    int nsplit = (int)std::min<long>(std::max<long>(1, (want + thr - 1) / thr), std::max(1, b.min_nd / 4));
+    dim3 grid(c.N / (vec * BC_TPB), b.n, nsplit);
+#define OB_BC2(C, NSV) do { if (vec == 2) OB_LAUNCH((baseconv_batch_kernel<C, NSV, 2>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); \
+                            else OB_LAUNCH((baseconv_batch_kernel<C, NSV, 1>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+#define OB_BC(NSV) do { if (centered) OB_BC2(true, NSV); else OB_BC2(false, NSV); } while (0)
     if (b.max_ns <= 1) OB_BC(1); else if (b.max_ns <= 2) OB_BC(2); else if (b.max_ns <= 3) OB_BC(3); else if (b.max_ns <= 4) OB_BC(4);
     else if (b.max_ns <= 6) OB_BC(6); else if (b.max_ns <= 8) OB_BC(8); else OB_BC(MAX_NS);
+#undef OB_BC2
 #undef OB_BC
 }
 
