@@ -209,6 +209,7 @@ ModConst make_modconst(u64 q) {
     m.r2 = mulmod_u64(m.r1, m.r1, q);    m.r2_sh = shoup_companion(m.r2, q);
     m.qd = (double)q;
     m.qinv_d = 1.0 / (double)q;
+    m.rinv_d = (double)invmod_u64(m.r1, q);
     m.one_sh = shoup_companion(1, q);
     return m;
 }

@@ -80,6 +80,7 @@ struct Context {
 struct NttPlan { const LimbDesc* first = nullptr; const LimbDesc* second = nullptr; int n = 0; };
 NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs);
 void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p);
+void ntt_forward_first(Context& c, const u64* in, u64* out, const NttPlan& p);   // strided pass only (lazy form), see ks_ntt2_inner_product
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p);
 
 }  // namespace ob

@@ -9,6 +9,7 @@
 // Limb-NTT count beta*W + L + 2K  (= SURVEY.md 8(d): beta(L+k) + 2L + 2k with the L own limbs never transformed).
 // Data flow of the reference GPU path for the same op: HE/src/heongpu/lib/host/ckks/operator.cu:1308-1429.
 #include "evaluator.h"
+#include <cstdlib>
 
 namespace ob {
 
@@ -111,7 +112,7 @@ void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, 
                    addend_period, addend_zstride);
 }
 
-void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits) {
+void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits, bool second_pass) {
     OB_CHECK(n >= 1 && n <= 4096, "decompose_n: polynomial count out of range");
     const KsPlan& p = ks_plan(level);
     const int L = p.L, K = p.K, W = p.W, beta = p.beta;
@@ -145,7 +146,16 @@ void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n,
     DevBuf coef((size_t)n * L * ctx.N * 8);
     ntt_inverse(ctx, c1s, coef.u(), dp.intt);
     base_convert_batch(ctx, dp.bc, coef.u(), digits, false);
-    ntt_forward(ctx, digits, digits, dp.ntt);
+    if (second_pass) ntt_forward(ctx, digits, digits, dp.ntt);
+    else ntt_forward_first(ctx, digits, digits, dp.ntt);
+}
+
+// The fused second-pass + inner-product kernel serialises the beta digits of a limb tile inside one CTA, so it needs
+// enough tiles to fill the GPU on its own: large rings / batches only.  ORION_B200_FUSED_IP=0/1 overrides.
+static bool use_fused_ip(const Context& c, int W, int n) {
+    const char* e = std::getenv("ORION_B200_FUSED_IP");
+    if (e && *e) return std::atoi(e) != 0;
+    return (long)(c.N >> 10) * W * n >= 148L * 8;
 }
 
 void PolyEvaluator::keyswitch(int level, const u64* c1_ntt, const u64* evk, const u64* addend, int addend_stride,
@@ -168,10 +178,12 @@ void PolyEvaluator::keyswitch_n(int level, int n, const u64* c1s, int c1_zstride
         const int m = std::min(chunk, n - z0);
         DevBuf digits((size_t)m * dw * 8), acc((size_t)m * 2 * p.W * N * 8);
         const u64* c1 = c1s + (size_t)z0 * c1_zstride * N;
-        decompose_n(level, c1, c1_zstride, m, digits.u());
+        const bool fused = use_fused_ip(ctx, p.W, m);
+        decompose_n(level, c1, c1_zstride, m, digits.u(), !fused);
         IpMulti im{};
         for (int z = 0; z < m; ++z) { im.evk[z] = evks[z0 + z]; im.scatter[z] = nullptr; }
-        ks_inner_product_multi(ctx, level, m, c1, (size_t)c1_zstride * N, digits.u(), dw, im, acc.u(), (size_t)2 * p.W * N, 0, nullptr, 0);
+        if (fused) ks_ntt2_inner_product(ctx, level, m, c1, (size_t)c1_zstride * N, digits.u(), dw, im, acc.u(), (size_t)2 * p.W * N);
+        else ks_inner_product_multi(ctx, level, m, c1, (size_t)c1_zstride * N, digits.u(), dw, im, acc.u(), (size_t)2 * p.W * N, 0, nullptr, 0);
         moddown_n(level, acc.u(), p.W, 2 * m, addend ? addend + (size_t)z0 * addend_zstride * N : nullptr, 0, addend ? 1 : 0,
                   out + (size_t)z0 * 2 * p.L * N, p.L, 2, addend_zstride);
     }

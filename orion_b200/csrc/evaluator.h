@@ -39,7 +39,7 @@ class PolyEvaluator {
 
     // ---- batched variants: n independent polynomials in one set of launches (hoisted BSGS giant steps) ----
     // c1s: polynomial z at c1s + z*c1_stride*N ([L][N]);  digits: [n][beta][W][N]
-    void decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits);
+    void decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits, bool second_pass = true);
     // acc: polynomial z at acc + z*acc_stride*N ([W][N] QP);  out: polynomial z at out + z*out_stride*N ([L][N])
     void moddown_n(int level, const u64* acc, int acc_stride, int n, const u64* addend, int addend_stride, int addend_polys,
                    u64* out, int out_stride, int addend_period = 0, int addend_zstride = 0);

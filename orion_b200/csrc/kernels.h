@@ -56,6 +56,10 @@ constexpr int IPM_MAX = 48;
 struct IpMulti { const u64* evk[IPM_MAX]; const uint32_t* scatter[IPM_MAX]; };
 void ks_inner_product_multi(Context& c, int level, int n, const u64* c1, size_t c1_zstride, const u64* digits, size_t dig_zstride,
                             const IpMulti& m, u64* out, size_t out_zstride, int add_mode, const u64* addend, size_t addend_zstride);
+// Same contraction with the second (contiguous) NTT pass of the digits fused in: `digits` holds the output of
+// ntt_forward_first.  Plain accumulate only (no addend, no automorphism).  ntt.cu.
+void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c1_zstride, const u64* digits, size_t dig_zstride,
+                           const IpMulti& m, u64* out, size_t out_zstride);
 // out[2][W][N] = sum of n QP ciphertexts
 constexpr int SUM_MAX = 64;
 struct SumList { const u64* p[SUM_MAX]; };

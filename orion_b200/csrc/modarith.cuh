@@ -32,6 +32,7 @@ struct ModConst {
     double qd;     // (double) q
     u64 one_sh;    // floor(2^64/q): Shoup companion of 1 (reduces any 64-bit value to [0,2q))
     double qinv_d; // 1.0 / (double) q, correctly rounded (FP64 butterfly path)
+    double rinv_d; // (double)(2^-64 mod q): takes a Montgomery factor out on the FP64 path (exact for q < 2^53)
 };
 
 #ifdef __CUDACC__

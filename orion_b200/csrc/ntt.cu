@@ -16,6 +16,7 @@
 // The reference GPU path (NT/src/lib/ntt_merge/ntt.cu:179,709) does one butterfly per thread per
 // __syncthreads with Barrett multiplication; this is a different design, not a port.
 #include "context.h"
+#include "kernels.h"
 
 namespace ob {
 
@@ -67,8 +68,13 @@ constexpr unsigned long long F64_EXP52 = 0x4330000000000000ull;   // bit pattern
 struct ArithInt {
     typedef u64 T;
     typedef ulonglong2 TW;
-    u64 q, q2;
-    __device__ __forceinline__ explicit ArithInt(const ModConst& m) : q(m.q), q2(2 * m.q) {}
+    typedef ulonglong2 Acc;                              // fused inner product: 128-bit lazy accumulator (x = low, y = high < q)
+    u64 q, q2, qinv_neg;
+    __device__ __forceinline__ explicit ArithInt(const ModConst& m) : q(m.q), q2(2 * m.q), qinv_neg(m.qinv_neg) {}
+    __device__ __forceinline__ Acc acc_zero() const { return make_ulonglong2(0, 0); }
+    __device__ __forceinline__ T keep(T x) const { return final_fwd(x); }
+    __device__ __forceinline__ void mac(Acc& a, T d, u64 k) const { mac128(a.y, a.x, d, k, q); }      // k in Montgomery form
+    __device__ __forceinline__ u64 acc_word(Acc a) const { return mont_redc(a.y, a.x, q, qinv_neg); }
     __device__ __forceinline__ T from_word(u64 x) const { return x; }          // normalised input word
     __device__ __forceinline__ T from_raw(u64 x) const { return x; }           // inter-pass / shared-memory word
     __device__ __forceinline__ u64 to_raw(T x) const { return x; }
@@ -98,8 +104,15 @@ struct ArithInt {
 struct ArithF64 {
     typedef double T;
     typedef double TW;
-    double q, qinv;
-    __device__ __forceinline__ explicit ArithF64(const ModConst& m) : q(m.qd), qinv(m.qinv_d) {}
+    typedef double Acc;                                  // fused inner product: sum of centred residues (|sum| < beta * 0.7q)
+    double q, qinv, rinv;
+    __device__ __forceinline__ explicit ArithF64(const ModConst& m) : q(m.qd), qinv(m.qinv_d), rinv(m.rinv_d) {}
+    __device__ __forceinline__ Acc acc_zero() const { return 0.0; }
+    __device__ __forceinline__ T keep(T x) const { recentre(x); return x; }
+    // k is a Montgomery-form word below q < 2^46: exact as a double, so d*k mod q is the same residue the integer path
+    // accumulates; the factor 2^-64 is taken out once at the end (acc_word)
+    __device__ __forceinline__ void mac(Acc& a, T d, u64 k) const { a = __dadd_rn(a, mulmod(d, from_word(k))); }
+    __device__ __forceinline__ u64 acc_word(Acc a) const { recentre(a); return to_word(mulmod(a, rinv)); }
     __device__ __forceinline__ T from_word(u64 x) const { return __dsub_rn(__longlong_as_double(x | F64_EXP52), 4503599627370496.0); }
     __device__ __forceinline__ T from_raw(u64 x) const { return __longlong_as_double(x); }
     __device__ __forceinline__ u64 to_raw(T x) const { return (u64)__double_as_longlong(x); }
@@ -217,9 +230,12 @@ __device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], 
 // FWD walks the transformed bits downwards, INV upwards.  Every transform is exactly two passes: the first one
 // (!FINAL) reads normalised words and leaves policy-specific lazy values, the second one (FINAL) normalises (and
 // scales by N^-1 for INV).
-template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL>
+// KEEP (contiguous forward final pass only): the results stay in registers -- thread tid returns words [8 tid, 8 tid + 8)
+// of the tile as policy values (A::keep) instead of storing them.
+template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL, bool KEEP = false>
 __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restrict__ src, u64* __restrict__ dst,
-                                         const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN) {
+                                         const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN,
+                                         typename A::T* kept = nullptr) {
     typedef typename A::T T;
     constexpr int LOG_EPT = log_ept(STRIDED, FWD), EPT = 1 << LOG_EPT;
     constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
@@ -296,7 +312,12 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
         else OB_RADIX(inv_radix, true, );
 #undef OB_RADIX
         done += nb;
-        if (r == NR - 1) {
+        if (KEEP && r == NR - 1) {
+            // last round of the contiguous pass: pos = 0, groups of 2^nb adjacent words, group g of thread tid at
+            // (tid * G + g) << nb  ->  element e sits at word tid * EPT + e
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) kept[e] = ar.keep(v[e]);
+        } else if (r == NR - 1) {
             u64 w[EPT];
 #pragma unroll
             for (int e = 0; e < EPT; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
@@ -338,6 +359,72 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
         ntt_body<ArithInt, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithInt(m), sm, src, dst, tw_all + (size_t)ld.mod * N, ni, logN);
 }
 
+// Fused second NTT pass + key-switch inner product (evaluator.cu step 3b + 4).  A CTA owns 1024 consecutive coefficients
+// of one QP limb t of ciphertext z and walks the beta digits: the digit's tile (left in lazy form by the strided pass)
+// goes through the 8 contiguous stages in shared memory, stays in registers, and is multiplied into the two
+// accumulators against the evaluation key.  The transformed digits are never written: 2 x beta*W limb moves per key
+// switch less than NTT + inner_product_multi_kernel, and the key stream (the compulsory traffic) overlaps the butterflies.
+// Own-digit limbs (t inside digit j) come straight from c1.  Two shared-memory tiles alternate so that a digit's first
+// exchange cannot overwrite words a slower warp still reads for the previous digit.
+struct LimbTab { unsigned char t[128]; };
+template <class A>
+__global__ void __launch_bounds__(1 << (LOG_E_CONTIG - 3))
+ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restrict__ digits, size_t dig_zstride,
+               const IpMulti m, u64* __restrict__ out, size_t out_zstride, const __grid_constant__ LimbTab tab,
+               int L, int K, int nQ, int nmod, int beta, const ModConst* __restrict__ mc,
+               const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN) {
+    OB_PDL_SYNC();
+    constexpr int EPT = 8, SM_WORDS = (1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3));
+    __shared__ __align__(16) u64 sm[2][SM_WORDS];
+    typedef typename A::T T;
+    const int t = tab.t[blockIdx.y], z = blockIdx.z, W = L + K;
+    const size_t N = (size_t)1 << logN;
+    const int ci = t < L ? t : nQ + (t - L);
+    const A ar(mc[ci]);
+    const int own = t < L ? t / K : -1;
+    const typename A::TW* tw;
+    if constexpr (sizeof(typename A::TW) == 8) tw = twd_all + (size_t)ci * N; else tw = tw_all + (size_t)ci * N;
+    const size_t off = ((size_t)blockIdx.x << LOG_E_CONTIG) + threadIdx.x * EPT;      // this thread's 8 words in the limb
+    const u64* __restrict__ evk = m.evk[z] + (size_t)ci * N + off;
+    const u64* __restrict__ c1t = c1 + (size_t)z * c1_zstride + (size_t)t * N + off;
+    const u64* __restrict__ dz = digits + (size_t)z * dig_zstride + (size_t)t * N;
+    typename A::Acc a0[EPT], a1[EPT];
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) { a0[e] = ar.acc_zero(); a1[e] = ar.acc_zero(); }
+    int buf = 0;
+    for (int j = 0; j < beta; ++j) {
+        T d[EPT];
+        if (j == own) {
+            u64 w[EPT];
+            ld_global_256(c1t, w[0], w[1], w[2], w[3]); ld_global_256(c1t + 4, w[4], w[5], w[6], w[7]);
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) d[e] = ar.from_word(w[e]);
+        } else {
+            ntt_body<A, LOG_E_CONTIG, K2_BITS, false, true, true, true>(ar, sm[buf], dz + (size_t)j * W * N, nullptr, tw,
+                                                                         make_ulonglong2(0, 0), logN, d);
+            buf ^= 1;
+        }
+        const u64* k0 = evk + (size_t)j * 2 * nmod * N;
+        const u64* k1 = k0 + (size_t)nmod * N;
+        u64 k[EPT];
+        ld_global_256(k0, k[0], k[1], k[2], k[3]); ld_global_256(k0 + 4, k[4], k[5], k[6], k[7]);
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) ar.mac(a0[e], d[e], k[e]);
+        ld_global_256(k1, k[0], k[1], k[2], k[3]); ld_global_256(k1 + 4, k[4], k[5], k[6], k[7]);
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) ar.mac(a1[e], d[e], k[e]);
+    }
+    u64* o0 = out + (size_t)z * out_zstride + (size_t)t * N + off;
+    u64* o1 = o0 + (size_t)W * N;
+    u64 r[EPT];
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) r[e] = ar.acc_word(a0[e]);
+    st_global_256(o0, r[0], r[1], r[2], r[3]); st_global_256(o0 + 4, r[4], r[5], r[6], r[7]);
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) r[e] = ar.acc_word(a1[e]);
+    st_global_256(o1, r[0], r[1], r[2], r[3]); st_global_256(o1 + 4, r[4], r[5], r[6], r[7]);
+}
+
 }  // namespace
 
 NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
@@ -370,6 +457,34 @@ void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p) {
     OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
     OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, true, true>), g2, 1 << (LOG_E_CONTIG - log_ept(false, true)), 0, stream(),
               (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
+}
+
+// First (strided) pass only: the limbs are left in the policy's lazy inter-pass form for ks_ntt2_inner_product.
+void ntt_forward_first(Context& c, const u64* in, u64* out, const NttPlan& p) {
+    if (p.n == 0) return;
+    const int s1 = c.logN - K2_BITS;
+    dim3 g1(c.N >> LOG_E_STRIDED, p.n);
+    OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
+}
+
+// acc[z][c][t] = sum_j NTT2(digits[z][j][t]) * evk_z[j][c][chain(t)]  -- see ntt2_ip_kernel.  One launch per arithmetic
+// policy (the FP64 instantiation needs half the accumulator registers of the integer one).
+void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c1_zstride, const u64* digits, size_t dig_zstride,
+                           const IpMulti& m, u64* out, size_t out_zstride) {
+    OB_CHECK(n >= 1 && n <= IPM_MAX, "inner product batch size");
+    const int L = level + 1, K = c.nP, W = L + K, beta = c.num_digits(level);
+    OB_CHECK(W <= 128 && beta <= 64, "fused inner product: chain too long");
+    LimbTab tf{}, ti{};
+    int nf = 0, ni = 0;
+    for (int t = 0; t < W; ++t) {
+        const int ci = t < L ? t : c.nQ + (t - L);
+        if (c.mc[ci].bits <= F64_MAX_BITS) tf.t[nf++] = (unsigned char)t; else ti.t[ni++] = (unsigned char)t;
+    }
+    const int tiles = c.N >> LOG_E_CONTIG, tpb = 1 << (LOG_E_CONTIG - 3);
+    if (nf) OB_LAUNCH((ntt2_ip_kernel<ArithF64>), dim3(tiles, nf, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
+                      out_zstride, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+    if (ni) OB_LAUNCH((ntt2_ip_kernel<ArithInt>), dim3(tiles, ni, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
+                      out_zstride, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
 }
 
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
