@@ -392,7 +392,16 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
 #pragma unroll
     for (int e = 0; e < EPT; ++e) { a0[e] = ar.acc_zero(); a1[e] = ar.acc_zero(); }
     int buf = 0;
+    // L2 prefetch, one 128-byte line per thread: the key tiles of digit j (2 x 8 KB) and the tile of digit j+1 (8 KB), so
+    // that the loads that follow the butterflies find their lines in L2 (the kernel runs at ~20 warps/SM; measured
+    // 3 998 -> 4 275 keyswitch/s; a longer prefetch distance measured the same)
+    const size_t line = ((size_t)blockIdx.x << LOG_E_CONTIG) + (threadIdx.x & 63) * 16;
+    const u64* pf_evk = m.evk[z] + ((size_t)(threadIdx.x >> 6) * nmod + ci) * N + line;
+    const u64* pf_dig = dz + line;
     for (int j = 0; j < beta; ++j) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_evk + (size_t)j * 2 * nmod * N));
+        if (threadIdx.x < 64 && j + 1 < beta && j + 1 != own)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_dig + (size_t)(j + 1) * W * N));
         T d[EPT];
         if (j == own) {
             u64 w[EPT];
