@@ -107,9 +107,9 @@ void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, 
     DevBuf pc((size_t)n * K * N * 8), conv((size_t)n * L * N * 8);
     ntt_inverse(ctx, acc, pc.u(), mp.intt);
     base_convert_batch(ctx, mp.bc, pc.u(), conv.u(), true);
-    ntt_forward(ctx, conv.u(), conv.u(), mp.ntt);
-    moddown_finish(ctx, level, acc, acc_stride, conv.u(), addend, addend_stride, addend_polys, out, out_stride, n,
-                   addend_period, addend_zstride);
+    ntt_forward_first(ctx, conv.u(), conv.u(), mp.ntt);
+    ntt2_submul(ctx, L, n, acc, acc_stride, conv.u(), ctx.d_pinv.as<ulonglong2>(), addend, addend_stride, addend_polys,
+                addend_period, addend_zstride, out, out_stride);
 }
 
 void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n, u64* digits, bool second_pass) {
@@ -207,8 +207,9 @@ void PolyEvaluator::rescale(int level, const u64* in, int in_stride, u64* out, i
     DevBuf last((size_t)polys * N * 8), tmp((size_t)polys * level * N * 8);
     ntt_inverse(ctx, in, last.u(), ci[key]);
     rescale_prep(ctx, level, last.u(), tmp.u(), polys);
-    ntt_forward(ctx, tmp.u(), tmp.u(), cf[key]);
-    rescale_finish(ctx, level, in, in_stride, tmp.u(), out, out_stride, polys);
+    ntt_forward_first(ctx, tmp.u(), tmp.u(), cf[key]);
+    ntt2_submul(ctx, level, polys, in, in_stride, tmp.u(), ctx.d_qlinv.as<ulonglong2>() + (size_t)level * ctx.nQ, nullptr, 0, 0, 0, 0,
+                out, out_stride);
 }
 
 }  // namespace ob

@@ -60,18 +60,16 @@ void ks_inner_product_multi(Context& c, int level, int n, const u64* c1, size_t 
 // ntt_forward_first.  Plain accumulate only (no addend, no automorphism).  ntt.cu.
 void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c1_zstride, const u64* digits, size_t dig_zstride,
                            const IpMulti& m, u64* out, size_t out_zstride);
+// Second NTT pass fused with the ModDown / rescale epilogue (ntt.cu): out = (a - NTT(b)) * mulc (+ addend).
+void ntt2_submul(Context& c, int nl, int polys, const u64* a, int a_stride, const u64* b, const ulonglong2* mulc,
+                 const u64* addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
+                 u64* out, int out_stride);
 // out[2][W][N] = sum of n QP ciphertexts
 constexpr int SUM_MAX = 64;
 struct SumList { const u64* p[SUM_MAX]; };
 void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out);
 
-// out[p][i][x] = (acc[p][i][x] - conv[p][i][x]) * P^-1 (+ addend[p][i][x])   i <= level; acc has stride W limbs
-void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
-                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys,
-                    int addend_period = 0, int addend_zstride = 0);   // period > 0: polynomial z*period + c gets addend (z, c), c < addend_polys
-
 // rescale helpers (level -> level-1): see evaluator.cu
 void rescale_prep(Context& c, int level, const u64* last_coeff /* [polys][N] */, u64* tmp /* [polys][level][N] */, int polys);
-void rescale_finish(Context& c, int level, const u64* in, int in_stride, const u64* tmp, u64* out, int out_stride, int polys);
 
 }  // namespace ob

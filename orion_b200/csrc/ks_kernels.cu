@@ -301,30 +301,6 @@ sum_qp_kernel(const SumList lst, int n, u64* __restrict__ out, int N, int L, int
     *(ulonglong2*)(out + o) = a;
 }
 
-__global__ void __launch_bounds__(TPB)
-moddown_finish_kernel(const u64* __restrict__ acc, int acc_stride, const u64* __restrict__ conv, int L,
-                      const u64* __restrict__ addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
-                      u64* __restrict__ out, int out_stride, int N,
-                      const ulonglong2* __restrict__ pinv, const ModConst* __restrict__ mc) {
-    OB_PDL_SYNC();
-    const int i = blockIdx.y, p = blockIdx.z;
-    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
-    const u64 q = mc[i].q;
-    const ulonglong2 w = pinv[i];
-    const ulonglong2 a = *(const ulonglong2*)(acc + ((size_t)p * acc_stride + i) * N + x);
-    const ulonglong2 b = *(const ulonglong2*)(conv + ((size_t)p * L + i) * N + x);
-    ulonglong2 r;
-    r.x = shoup_mul(sub_mod(a.x, b.x, q), w.x, w.y, q);
-    r.y = shoup_mul(sub_mod(a.y, b.y, q), w.x, w.y, q);
-    // polynomial p = z*period + c receives addend polynomial c of group z when c < addend_polys
-    const int pz = p / addend_period, pc = p - pz * addend_period;
-    if (addend != nullptr && pc < addend_polys) {
-        const ulonglong2 e = *(const ulonglong2*)(addend + ((size_t)pz * addend_zstride + (size_t)pc * addend_stride + i) * N + x);
-        r.x = add_mod(r.x, e.x, q); r.y = add_mod(r.y, e.y, q);
-    }
-    *(ulonglong2*)(out + ((size_t)p * out_stride + i) * N + x) = r;
-}
-
 // tmp[p][i][x] = ((last[p][x] + (q_l-1)/2) mod q_l) mod q_i - ((q_l-1)/2 mod q_i)        (coefficient domain)
 __global__ void __launch_bounds__(TPB)
 rescale_prep_kernel(const u64* __restrict__ last, u64* __restrict__ tmp, int level, int N,
@@ -338,24 +314,6 @@ rescale_prep_kernel(const u64* __restrict__ last, u64* __restrict__ tmp, int lev
     const u64 u = barrett_red(0, s, m), hq = barrett_red(0, half, m);
     tmp[((size_t)p * level + i) * N + x] = sub_mod(u, hq, m.q);
 }
-// out[p][i][x] = (in[p][i][x] - tmp[p][i][x]) * q_l^-1 mod q_i
-__global__ void __launch_bounds__(TPB)
-rescale_finish_kernel(const u64* __restrict__ in, int in_stride, const u64* __restrict__ tmp,
-                      u64* __restrict__ out, int out_stride, int level, int N,
-                      const ulonglong2* __restrict__ qlinv_row, const ModConst* __restrict__ mc) {
-    OB_PDL_SYNC();
-    const int i = blockIdx.y, p = blockIdx.z;
-    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
-    const u64 q = mc[i].q;
-    const ulonglong2 w = qlinv_row[i];
-    const ulonglong2 a = *(const ulonglong2*)(in + ((size_t)p * in_stride + i) * N + x);
-    const ulonglong2 b = *(const ulonglong2*)(tmp + ((size_t)p * level + i) * N + x);
-    ulonglong2 r;
-    r.x = shoup_mul(sub_mod(a.x, b.x, q), w.x, w.y, q);
-    r.y = shoup_mul(sub_mod(a.y, b.y, q), w.x, w.y, q);
-    *(ulonglong2*)(out + ((size_t)p * out_stride + i) * N + x) = r;
-}
-
 }  // namespace
 
 BaseConvPlan make_baseconv_plan(Context& c, const std::vector<int>& src, const std::vector<int>& dst,
@@ -454,22 +412,9 @@ void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out) {
     OB_LAUNCH(sum_qp_kernel, grid, TPB, 0, stream(), lst, n, out, c.N, L, W, c.nQ, c.dmc());
 }
 
-void moddown_finish(Context& c, int level, const u64* acc, int acc_stride, const u64* conv, const u64* addend,
-                    int addend_stride, int addend_polys, u64* out, int out_stride, int polys, int addend_period, int addend_zstride) {
-    dim3 grid(c.N / (2 * TPB), level + 1, polys);
-    if (addend_period <= 0) { addend_period = 1 << 30; addend_zstride = 0; }
-    OB_LAUNCH(moddown_finish_kernel, grid, TPB, 0, stream(), acc, acc_stride, conv, level + 1, addend, addend_stride,
-              addend_polys, addend_period, addend_zstride, out, out_stride, c.N, c.d_pinv.as<ulonglong2>(), c.dmc());
-}
-
 void rescale_prep(Context& c, int level, const u64* last_coeff, u64* tmp, int polys) {
     dim3 grid(c.N / TPB, level, polys);
     OB_LAUNCH(rescale_prep_kernel, grid, TPB, 0, stream(), last_coeff, tmp, level, c.N, c.dmc());
-}
-void rescale_finish(Context& c, int level, const u64* in, int in_stride, const u64* tmp, u64* out, int out_stride, int polys) {
-    dim3 grid(c.N / (2 * TPB), level, polys);
-    OB_LAUNCH(rescale_finish_kernel, grid, TPB, 0, stream(), in, in_stride, tmp, out, out_stride, level, c.N,
-              c.d_qlinv.as<ulonglong2>() + (size_t)level * c.nQ, c.dmc());
 }
 
 }  // namespace ob

@@ -73,6 +73,7 @@ struct ArithInt {
     __device__ __forceinline__ explicit ArithInt(const ModConst& m) : q(m.q), q2(2 * m.q), qinv_neg(m.qinv_neg) {}
     __device__ __forceinline__ Acc acc_zero() const { return make_ulonglong2(0, 0); }
     __device__ __forceinline__ T keep(T x) const { return final_fwd(x); }
+    __device__ __forceinline__ u64 kept_word(T x) const { return x; }
     __device__ __forceinline__ void mac(Acc& a, T d, u64 k) const { mac128(a.y, a.x, d, k, q); }      // k in Montgomery form
     __device__ __forceinline__ u64 acc_word(Acc a) const { return mont_redc(a.y, a.x, q, qinv_neg); }
     __device__ __forceinline__ T from_word(u64 x) const { return x; }          // normalised input word
@@ -109,6 +110,7 @@ struct ArithF64 {
     __device__ __forceinline__ explicit ArithF64(const ModConst& m) : q(m.qd), qinv(m.qinv_d), rinv(m.rinv_d) {}
     __device__ __forceinline__ Acc acc_zero() const { return 0.0; }
     __device__ __forceinline__ T keep(T x) const { recentre(x); return x; }
+    __device__ __forceinline__ u64 kept_word(T x) const { return to_word(x); }
     // k is a Montgomery-form word below q < 2^46: exact as a double, so d*k mod q is the same residue the integer path
     // accumulates; the factor 2^-64 is taken out once at the end (acc_word)
     __device__ __forceinline__ void mac(Acc& a, T d, u64 k) const { a = __dadd_rn(a, mulmod(d, from_word(k))); }
@@ -434,6 +436,52 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
     st_global_256(o1, r[0], r[1], r[2], r[3]); st_global_256(o1 + 4, r[4], r[5], r[6], r[7]);
 }
 
+// Fused second NTT pass + "subtract and scale" epilogue shared by ModDown and rescale:
+//   out[p][i] = (a[p][i] - NTT(b[p][i])) * mulc[i]  (+ addend)      mod q_i
+// b holds the output of ntt_forward_first; the transformed limb is never written.
+template <class A>
+__device__ __forceinline__ void ntt2_submul_body(const A ar, u64* sm, const u64* __restrict__ a, const u64* __restrict__ b,
+                                                 const u64* __restrict__ addend, u64* __restrict__ out,
+                                                 const typename A::TW* __restrict__ tw, const ulonglong2 w, const u64 q, int logN) {
+    constexpr int EPT = 8;
+    typename A::T d[EPT];
+    ntt_body<A, LOG_E_CONTIG, K2_BITS, false, true, true, true>(ar, sm, b, nullptr, tw, make_ulonglong2(0, 0), logN, d);
+    const size_t off = ((size_t)blockIdx.x << LOG_E_CONTIG) + threadIdx.x * EPT;
+    u64 x[EPT], r[EPT];
+    ld_global_256(a + off, x[0], x[1], x[2], x[3]); ld_global_256(a + off + 4, x[4], x[5], x[6], x[7]);
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) r[e] = shoup_mul(sub_mod(x[e], ar.kept_word(d[e]), q), w.x, w.y, q);
+    if (addend != nullptr) {
+        ld_global_256(addend + off, x[0], x[1], x[2], x[3]); ld_global_256(addend + off + 4, x[4], x[5], x[6], x[7]);
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) r[e] = add_mod(r[e], x[e], q);
+    }
+    st_global_256(out + off, r[0], r[1], r[2], r[3]); st_global_256(out + off + 4, r[4], r[5], r[6], r[7]);
+}
+
+__global__ void __launch_bounds__(1 << (LOG_E_CONTIG - 3))
+ntt2_submul_kernel(const u64* __restrict__ a, int a_stride, const u64* __restrict__ b, int nl,
+                   const u64* __restrict__ addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
+                   u64* __restrict__ out, int out_stride, const ulonglong2* __restrict__ mulc, const ModConst* __restrict__ mc,
+                   const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN) {
+    OB_PDL_SYNC();
+    __shared__ __align__(16) u64 sm[(1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3))];
+    const int i = blockIdx.y, p = blockIdx.z;
+    const size_t N = (size_t)1 << logN;
+    const ModConst& m = mc[i];
+    // polynomial p = z*period + c receives addend polynomial c of group z when c < addend_polys
+    const int pz = p / addend_period, pc = p - pz * addend_period;
+    const u64* ad = (addend != nullptr && pc < addend_polys)
+                        ? addend + ((size_t)pz * addend_zstride + (size_t)pc * addend_stride + i) * N : nullptr;
+    const u64* ap = a + ((size_t)p * a_stride + i) * N;
+    const u64* bp = b + ((size_t)p * nl + i) * N;
+    u64* op = out + ((size_t)p * out_stride + i) * N;
+    if (m.bits <= F64_MAX_BITS)
+        ntt2_submul_body<ArithF64>(ArithF64(m), sm, ap, bp, ad, op, twd_all + (size_t)i * N, mulc[i], m.q, logN);
+    else
+        ntt2_submul_body<ArithInt>(ArithInt(m), sm, ap, bp, ad, op, tw_all + (size_t)i * N, mulc[i], m.q, logN);
+}
+
 }  // namespace
 
 NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
@@ -494,6 +542,16 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
                       out_zstride, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
     if (ni) OB_LAUNCH((ntt2_ip_kernel<ArithInt>), dim3(tiles, ni, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
                       out_zstride, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+}
+
+// out[p][i] = (a[p*a_stride + i] - NTT(b[p*nl + i])) * mulc[i] (+ addend), limbs i < nl of the Q chain, b from ntt_forward_first
+void ntt2_submul(Context& c, int nl, int polys, const u64* a, int a_stride, const u64* b, const ulonglong2* mulc,
+                 const u64* addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
+                 u64* out, int out_stride) {
+    if (addend_period <= 0) { addend_period = 1 << 30; addend_zstride = 0; }
+    OB_LAUNCH(ntt2_submul_kernel, dim3(c.N >> LOG_E_CONTIG, nl, polys), 1 << (LOG_E_CONTIG - 3), 0, stream(), a, a_stride, b, nl,
+              addend, addend_stride, addend_polys, addend_period, addend_zstride, out, out_stride, mulc, c.dmc(),
+              c.tw_fwd(), c.twd_fwd(), c.logN);
 }
 
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
