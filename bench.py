@@ -211,15 +211,26 @@ def main():
     for s in range(args.warmup):
         step_resident(s)
     sampler = ClockSampler(local) if rank == 0 else None
+    lib.B200_ProbeEnable(1)                             # CUDA events around the dominant kernel, on its own stream
     ms, launches = timed(step_resident, args.steps)
+    lib.B200_ProbeEnable(0)
+    probe_n = ctypes.c_long(0)
+    probe_ms = lib.B200_ProbeReadMs(ctypes.byref(probe_n))
     clocks = sampler.stop() if sampler else None
     for s in range(max(1, args.warmup // 2)):
         step_e2e(s)
     e2e_steps = max(2, args.steps // 4)
     ms_e2e, _ = timed(step_e2e, e2e_steps)
 
-    # roofline of the dominant kernel class: the batched NTT over the converted digit limbs (beta*W - L limbs),
-    # timed alone with CUDA events on the library stream, inputs 99 MB per launch pair cycled over > L2
+    # roofline of the dominant kernel: ntt2_ip_kernel<ArithF64> -- second NTT pass of the converted digits fused with the
+    # evaluation-key inner product, over the nf limbs of at most 46 bits.  Algorithmic bytes per launch (GROUP
+    # ciphertexts): per limb beta digit tiles in (own-digit tiles come from c1), 2*beta key tiles in, 2 accumulator tiles out.
+    nf = sum(1 for q in list(Q) + list(P) if int(q).bit_length() <= 46)
+    ip_bytes = 8 * N * GROUP * nf * (3 * beta + 2)
+    ip_ms = probe_ms / max(1, probe_n.value)
+    ip_gbs = ip_bytes / (ip_ms * 1e-3) / 1e9 if probe_n.value else 0.0
+    # secondary: the stand-alone batched NTT over the converted digit limbs (beta*W - L limbs), timed alone with CUDA
+    # events on the library stream, inputs 99 MB per launch pair cycled over > L2
     nl = beta * nmod - L
     mods = [(i % nmod) for i in range(nl)]
     big = [lib.B200_DevAlloc(nl * N) for _ in range(3)]            # 3 x 100 MB working sets
@@ -240,9 +251,10 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic = None
+    traffic = ntt_traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "ntt_traffic.json")))["dram_bytes_per_launch"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ks_fused_traffic.json")))["dram_bytes_per_launch"]
+        ntt_traffic = json.load(open(os.path.join(ROOT, "profiles", "ntt_traffic.json")))["dram_bytes_per_launch"]
     except Exception:
         pass
     ntt_gbs = ntt_bytes / (ntt_ms * 1e-3) / 1e9
@@ -282,11 +294,15 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * 2 * LN * 8,
                     "d2h_bytes_per_step": BATCH * 2 * LN * 8},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "ntt_pass (forward NTT of the %d converted digit limbs, 2 launches)" % nl,
-                         "achieved": ntt_gbs, "peak": peak, "unit": "GB/s", "frac": ntt_gbs / peak,
+            "roofline": {"bound": "hbm", "kernel": "ntt2_ip_kernel<ArithF64> (second NTT pass of the digits fused with the evaluation-key inner product; %d limbs x %d ciphertexts per launch)" % (nf, GROUP),
+                         "achieved": ip_gbs, "peak": peak, "unit": "GB/s", "frac": ip_gbs / peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                         "algorithmic_bytes_per_launch": ntt_bytes // 2, "launches": 2,
-                         "traffic": traffic, "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture (profiles/ntt_traffic.json)"},
+                         "algorithmic_bytes_per_launch": ip_bytes, "launches": int(probe_n.value), "avg_launch_us": ip_ms * 1e3,
+                         "share_of_step": probe_ms / ms if ms else None,
+                         "traffic": traffic, "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture (profiles/ks_fused_traffic.json)"},
+            "ntt_roofline": {"bound": "hbm", "kernel": "ntt_pass (stand-alone forward NTT of %d limbs, 2 launches)" % nl,
+                             "achieved": ntt_gbs, "peak": peak, "unit": "GB/s", "frac": ntt_gbs / peak,
+                             "algorithmic_bytes_per_launch": ntt_bytes // 2, "launches": 2, "traffic": ntt_traffic},
             "clocks": clocks,
         }
         if cpu:

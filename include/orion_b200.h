@@ -44,6 +44,11 @@ unsigned long long B200_LaunchCount(void);                   /* kernels launched
 void*    B200_Stream(void);                                  /* cudaStream_t all work is issued on */
 void     B200_TimerStart(void);                              /* CUDA events on that stream */
 float    B200_TimerStopMs(void);
+/* Kernel probe: while enabled, every launch of the key switch's dominant kernel (fused second NTT pass + evaluation-key
+ * inner product, FP64-path limbs) is bracketed by CUDA events on its own stream; ReadMs returns the summed kernel time
+ * and the launch count since the last read.  Measurement aid for bench.py's roofline object. */
+void     B200_ProbeEnable(int on);
+double   B200_ProbeReadMs(long* launches);
 void*    B200_DevAlloc(size_t words);
 void     B200_DevFree(void* dev);
 void     B200_Upload(void* dev, const uint64_t* host, size_t words);

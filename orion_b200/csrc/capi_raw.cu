@@ -67,6 +67,8 @@ float B200_TimerStopMs(void) {
     float ms = 0; OB_CUDA(cudaEventElapsedTime(&ms, g_ev0, g_ev1));
     return ms;
 }
+void B200_ProbeEnable(int on) { probe_enable(on != 0); }
+double B200_ProbeReadMs(long* launches) { return probe_read_ms(launches); }
 
 void* B200_DevAlloc(size_t words) { ensure_device(); void* p; OB_CUDA(cudaMallocAsync(&p, words * 8, stream())); return p; }
 void B200_DevFree(void* p) { if (p) OB_CUDA(cudaFreeAsync(p, stream())); }

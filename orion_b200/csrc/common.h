@@ -32,6 +32,12 @@ extern unsigned long long g_launches;
 // completed and flushed.  Overlaps the tail wave of large kernels with the head of the next; policy in context.cu
 // (pdl_enabled: on for logN >= 15, ORION_B200_PDL=0/1 overrides).
 bool pdl_enabled();
+// Kernel probe: while enabled, the launcher of the key switch's dominant kernel brackets it with CUDA events on its own
+// stream (bench.py's roofline.achieved); probe_read sums the elapsed times and clears the list.
+void probe_enable(bool on);
+void probe_begin();
+void probe_end();
+double probe_read_ms(long* launches);
 bool dry_run();        // ORION_B200_DRYRUN=1: skip the launches (host-side enqueue cost measurement only; results are garbage)
 template <class... KArgs, class... Args>
 inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {

@@ -44,6 +44,35 @@ bool pdl_enabled() {
     if (forced == -2) { const char* s = std::getenv("ORION_B200_PDL"); forced = s ? (std::atoi(s) != 0) : -1; }
     return forced >= 0 ? forced == 1 : g_pdl_auto;
 }
+namespace {
+bool g_probe_on = false;
+std::vector<std::pair<cudaEvent_t, cudaEvent_t>>& probe_events() { static auto* v = new std::vector<std::pair<cudaEvent_t, cudaEvent_t>>(); return *v; }
+}
+void probe_enable(bool on) { g_probe_on = on; }
+void probe_begin() {
+    if (!g_probe_on) return;
+    cudaEvent_t a, b;
+    OB_CUDA(cudaEventCreate(&a)); OB_CUDA(cudaEventCreate(&b));
+    OB_CUDA(cudaEventRecord(a, stream()));
+    probe_events().push_back({a, b});
+}
+void probe_end() {
+    if (!g_probe_on) return;
+    OB_CUDA(cudaEventRecord(probe_events().back().second, stream()));
+}
+double probe_read_ms(long* launches) {
+    double tot = 0;
+    auto& ev = probe_events();
+    for (auto& e : ev) {
+        OB_CUDA(cudaEventSynchronize(e.second));
+        float ms = 0; OB_CUDA(cudaEventElapsedTime(&ms, e.first, e.second));
+        tot += ms;
+        cudaEventDestroy(e.first); cudaEventDestroy(e.second);
+    }
+    if (launches) *launches = (long)ev.size();
+    ev.clear();
+    return tot;
+}
 bool dry_run() {
     static int on = -1;
     if (on < 0) { const char* s = std::getenv("ORION_B200_DRYRUN"); on = (s && std::atoi(s) != 0) ? 1 : 0; }

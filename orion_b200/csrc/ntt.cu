@@ -538,8 +538,12 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
         if (c.mc[ci].bits <= F64_MAX_BITS) tf.t[nf++] = (unsigned char)t; else ti.t[ni++] = (unsigned char)t;
     }
     const int tiles = c.N >> LOG_E_CONTIG, tpb = 1 << (LOG_E_CONTIG - 3);
-    if (nf) OB_LAUNCH((ntt2_ip_kernel<ArithF64>), dim3(tiles, nf, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
-                      out_zstride, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+    if (nf) {
+        probe_begin();
+        OB_LAUNCH((ntt2_ip_kernel<ArithF64>), dim3(tiles, nf, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
+                  out_zstride, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        probe_end();
+    }
     if (ni) OB_LAUNCH((ntt2_ip_kernel<ArithInt>), dim3(tiles, ni, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
                       out_zstride, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
 }
