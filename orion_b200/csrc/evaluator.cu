@@ -34,10 +34,13 @@ const KsPlan& PolyEvaluator::ks_plan(int level) {
             if (t >= s0 && t < s1) continue;
             int ci = t < L ? t : c.nQ + (t - L);
             dst.push_back(ci); off.push_back(j * W + t);
-            dl.push_back(LimbDesc{(uint32_t)(j * W + t), (uint32_t)(j * W + t), (uint32_t)ci, 0});
         }
         p->modup.push_back(make_baseconv_plan(c, src, dst, off));
         p->digit_src_off.push_back(s0);
+        const BaseConv& bc = *p->modup.back().bc;
+        for (size_t d = 0; d < dst.size(); ++d)
+            dl.push_back(LimbDesc{(uint32_t)off[d], (uint32_t)off[d], (uint32_t)dst[d],
+                                  bc_raw_out(bc.f64_src, bc.ns, c.mc[dst[d]].bits) ? 1u : 0u});
     }
     p->ntt_digits = make_ntt_plan(c, dl);
     p->modup_all = make_baseconv_batch(c, p->modup, p->digit_src_off, std::vector<int>(beta, 0));
@@ -132,7 +135,8 @@ void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n,
                     if (t >= s0 && t < s1) continue;
                     const int ci = t < L ? t : ctx.nQ + (t - L);
                     const uint32_t o = (uint32_t)((z * beta + j) * W + t);
-                    dl.push_back(LimbDesc{o, o, (uint32_t)ci, 0});
+                    const BaseConv& bc = *p.modup[j].bc;
+                    dl.push_back(LimbDesc{o, o, (uint32_t)ci, bc_raw_out(bc.f64_src, bc.ns, ctx.mc[ci].bits) ? 1u : 0u});
                 }
                 pl.push_back(p.modup[j]); io.push_back(z * L + s0); ob.push_back(z * beta * W);
             }

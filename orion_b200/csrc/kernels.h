@@ -25,6 +25,11 @@ void to_montgomery(Context& c, const u64* in, u64* out, int polys, int limbs, in
 void from_montgomery(Context& c, const u64* in, u64* out, int polys, int limbs, int L);
 
 // ---- base conversion: in [ns][N] (coefficient domain, contiguous), out limb d written at out + out_off[d]*N ----
+// A non-centred batched conversion (ModUp) whose sources and destination all run on the FP64 path leaves that
+// destination limb as the UNREDUCED sum of centred residues in double form (|value| <= (1 + 0.7 ns) q): the forward NTT
+// that always follows reads it as its lazy input (LimbDesc::aux bit 0) -- saves the final reduction here and the
+// word->double conversion there.  ns <= 4 keeps the NTT's growth bound (ntt.cu) intact.
+inline bool bc_raw_out(bool f64_src, int ns, int dst_bits) { return f64_src && ns <= 4 && dst_bits <= 46; }
 struct BaseConvPlan { const BaseConv* bc = nullptr; const LimbDesc* out_off = nullptr; };
 BaseConvPlan make_baseconv_plan(Context& c, const std::vector<int>& src, const std::vector<int>& dst,
                                 const std::vector<int>& out_off);

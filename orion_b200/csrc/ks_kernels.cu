@@ -172,12 +172,17 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
                         a[c] = __dadd_rn(a[c], __dadd_rn(__fma_rn(-tq, qd, h), l));
                     }
                 }
+            if (ns <= 4) {                       // bc_raw_out(): the NTT that follows takes the unreduced double as it is
 #pragma unroll
-            for (int c = 0; c < VEC; ++c) {
-                const double tq = __dsub_rn(__fma_rn(a[c], qinv, M), M);
-                double ac = __fma_rn(-tq, qd, a[c]);
-                ac = ac < 0.0 ? __dadd_rn(ac, qd) : ac;
-                r[c] = (u64)__double_as_longlong(__dadd_rn(ac, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+                for (int c = 0; c < VEC; ++c) r[c] = (u64)__double_as_longlong(a[c]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < VEC; ++c) {
+                    const double tq = __dsub_rn(__fma_rn(a[c], qinv, M), M);
+                    double ac = __fma_rn(-tq, qd, a[c]);
+                    ac = ac < 0.0 ? __dadd_rn(ac, qd) : ac;
+                    r[c] = (u64)__double_as_longlong(__dadd_rn(ac, 4503599627370496.0)) & 0x000FFFFFFFFFFFFFull;
+                }
             }
         } else {
             u64 hi[VEC], lo[VEC];

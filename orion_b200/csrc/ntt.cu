@@ -237,7 +237,7 @@ __device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], 
 template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL, bool KEEP = false>
 __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restrict__ src, u64* __restrict__ dst,
                                          const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN,
-                                         typename A::T* kept = nullptr) {
+                                         typename A::T* kept = nullptr, const bool raw_in = false) {
     typedef typename A::T T;
     constexpr int LOG_EPT = log_ept(STRIDED, FWD), EPT = 1 << LOG_EPT;
     constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
@@ -298,7 +298,7 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
                 for (int e = 0; e < EPT; ++e) w[e] = src[goff(e)];
             }
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) v[e] = FINAL ? ar.from_raw(w[e]) : ar.from_word(w[e]);
+            for (int e = 0; e < EPT; ++e) v[e] = (FINAL || raw_in) ? ar.from_raw(w[e]) : ar.from_word(w[e]);
         } else {
 #pragma unroll
             for (int e = 0; e < EPT; ++e) v[e] = ar.from_raw(sm[soff(e)]);
@@ -355,8 +355,10 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
     const u64* src = in + (size_t)ld.in_off * N;
     u64* dst = out + (size_t)ld.out_off * N;
     const ulonglong2 ni = ninv_all[ld.mod];
+    // aux bit 0 (forward first pass only): the limb already holds the FP64 policy's lazy values (kernels.h bc_raw_out)
     if (m.bits <= F64_MAX_BITS)
-        ntt_body<ArithF64, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithF64(m), sm, src, dst, twd_all + (size_t)ld.mod * N, ni, logN);
+        ntt_body<ArithF64, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithF64(m), sm, src, dst, twd_all + (size_t)ld.mod * N, ni, logN,
+                                                              nullptr, FWD && !FINAL && (ld.aux & 1));
     else
         ntt_body<ArithInt, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithInt(m), sm, src, dst, tw_all + (size_t)ld.mod * N, ni, logN);
 }
