@@ -2,6 +2,7 @@
 // conversion, key switching, rescale on host or device buffers.  This is the surface the primitive sweep
 // (BASELINE.json configs[4]) and the kernel parity tests drive; the Orion-facing surface with the Go shim's
 // export names lives in capi.cu.  Declarations + reference citations: include/orion_b200.h.
+#include <cstdlib>
 #include "evaluator.h"
 #include "../../include/orion_b200.h"
 
@@ -177,7 +178,10 @@ void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in
     const int L = level + 1;
     const size_t LN = (size_t)L * r->ctx->N;
     const size_t in_words = has_c0 ? 2 * LN : LN;
-    constexpr int NBUF = 3, GROUP = 4;                      // ciphertexts per pipeline stage
+    // ciphertexts per pipeline stage: the first upload and the last download are not overlapped with anything, so small
+    // stages shorten the fill/drain of the pipeline; compute has ~2x headroom over PCIe even at 2 per launch sequence
+    constexpr int NBUF = 4;
+    static const int GROUP = [] { const char* e = std::getenv("ORION_B200_E2E_GROUP"); int g = e ? std::atoi(e) : 2; return g < 1 ? 1 : (g > 8 ? 8 : g); }();
     static cudaStream_t s_up = nullptr, s_down = nullptr;
     static cudaEvent_t up_done[NBUF], comp_done[NBUF], down_done[NBUF];
     static size_t slot_words = 0;
@@ -205,8 +209,10 @@ void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in
     OB_CUDA(cudaStreamWaitEvent(s_up, start, 0));
     OB_CUDA(cudaStreamWaitEvent(s_down, start, 0));
     int g = 0;
-    for (int i0 = 0; i0 < n; i0 += GROUP, ++g) {
-        const int m = std::min(GROUP, n - i0), sl = g % NBUF;
+    for (int i0 = 0, m = 0; i0 < n; i0 += m, ++g) {
+        // single ciphertexts at both ends of the batch (shortest possible un-overlapped upload / download), GROUP in between
+        m = (g < 2 || n - i0 <= 2) ? 1 : std::min(GROUP, n - i0 - 2);
+        const int sl = g % NBUF;
         if (g >= NBUF) OB_CUDA(cudaStreamWaitEvent(s_up, comp_done[sl], 0));          // slot input free again
         for (int z = 0; z < m; ++z)
             OB_CUDA(cudaMemcpyAsync((u64*)d_in[sl] + (size_t)z * in_words, ct_in[i0 + z], in_words * 8, cudaMemcpyHostToDevice, s_up));
