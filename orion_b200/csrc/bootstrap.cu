@@ -263,6 +263,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
             while (b.encoded.size() > 6) {
                 auto old = b.encoded.begin();
                 for (auto i = b.encoded.begin(); i != b.encoded.end(); ++i) if (i->second.last_use < old->second.last_use) old = i;
+                OB_CUDA(cudaDeviceSynchronize());                 // bootstraps on other lanes may still read these factors
                 b.encoded.erase(old);
             }
         }
@@ -304,6 +305,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
             cur = cur * ps / bs.q_at(lvl);
         }
         b.built_for_scale = eff;
+        OB_CUDA(cudaStreamSynchronize(stream()));             // encoded on this lane, read by every later bootstrap on any lane
     }
 
     // ---- CoeffsToSlots ----

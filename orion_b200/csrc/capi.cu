@@ -36,6 +36,137 @@ int push_pt(std::unique_ptr<Plaintext> p) { return S().pts.add(std::move(p)); }
 Ciphertext& CT(int id) { return S().cts.get(id, "ciphertext"); }
 Plaintext& PT(int id) { return S().pts.get(id, "plaintext"); }
 std::unique_ptr<Ciphertext> fresh() { return std::make_unique<Ciphertext>(); }
+
+// ---- dataflow lanes -------------------------------------------------------------------------------------------
+// The reference's Python layer issues one backend call per ciphertext (`for id in tensor.ids: EvaluatePolynomial(id)`,
+// PY/poly_evaluator.py:28-31, PY/lt_evaluator.py:172-193); the calls on different ciphertexts of a tensor are
+// independent, and at logN = 13 one call cannot fill a B200.  Every evaluator entry point therefore runs on the stream
+// its operands live on ("follow the data"); a heavy call (bootstrap, polynomial, linear transform, key switch) whose
+// operands are all settled on the main stream opens the next lane.  A handle remembers the event of its last writer
+// (waited for by consumers on other lanes) and the events of readers on other lanes (waited for by the next writer and
+// by the free).  The main stream never waits on a lane, so it stays a cheap fork point; host-visible results
+// (Decrypt, Export*) synchronise the lane they ran on.  ORION_B200_ASYNC=0 keeps everything on the main stream.
+constexpr int NLANES = 8;
+cudaStream_t g_lanes[NLANES];
+int g_lanes_ready = 0, g_next_lane = 0;
+bool lanes_enabled() {
+    static int on = -1;
+    if (on < 0) { const char* e = std::getenv("ORION_B200_ASYNC"); on = (e && std::atoi(e) == 0) ? 0 : 1; if (!stream_fork_enabled()) on = 0; }
+    return on == 1;
+}
+cudaStream_t lane(int i) {
+    if (!g_lanes_ready) {
+        ensure_device();
+        for (int k = 0; k < NLANES; ++k) OB_CUDA(cudaStreamCreateWithFlags(&g_lanes[k], cudaStreamNonBlocking));
+        g_lanes_ready = 1;
+    }
+    return g_lanes[i % NLANES];
+}
+EvRef* const g_tail = new EvRef[NLANES];                  // last event recorded on each lane (leaked: no destructor order at exit)
+int lane_index(cudaStream_t s) { for (int k = 0; k < NLANES; ++k) if (g_lanes_ready && g_lanes[k] == s) return k; return -1; }
+cudaStream_t pick_lane() {                                // an idle lane if there is one, else round-robin
+    lane(0);
+    for (int k = 0; k < NLANES; ++k) {
+        const int c = (g_next_lane + k) % NLANES;
+        if (!g_tail[c] || cudaEventQuery(g_tail[c]->e) == cudaSuccess) { g_next_lane = c + 1; return g_lanes[c]; }
+    }
+    (void)cudaGetLastError();
+    return g_lanes[g_next_lane++ % NLANES];
+}
+void wait_on(cudaStream_t s, const EvRef& e) { if (e) OB_CUDA(cudaStreamWaitEvent(s, e->e, 0)); }
+void prune(std::vector<EvRef>& v) {                       // drop reader events that have completed
+    size_t k = 0;
+    for (auto& e : v) if (cudaEventQuery(e->e) != cudaSuccess) v[k++] = e;
+    v.resize(k);
+    (void)cudaGetLastError();                             // cudaErrorNotReady is not an error
+}
+
+struct Op {
+    cudaStream_t s = nullptr;                             // nullptr: the main stream
+    std::vector<Track*> reads, writes;
+    Op(bool heavy, std::initializer_list<Track*> w, std::initializer_list<Track*> r) : reads(r), writes(w) {
+        if (lanes_enabled()) {
+            // follow the data while the operand is the last thing queued on its lane (a true chain); once that lane has
+            // moved on (a sibling consumer of the same operand was queued there) take another lane and wait for the operand
+            Track* first = nullptr;
+            for (Track* t : writes) if (!first && t->ready) first = t;
+            for (Track* t : reads) if (!first && t->ready) first = t;
+            if (first) {
+                const int h = lane_index(first->home);
+                s = (h >= 0 && g_tail[h] == first->ready) ? first->home : pick_lane();
+            } else if (heavy) {
+                s = pick_lane();
+            }
+        }
+        cudaStream_t run = s ? s : main_stream();
+        if (s) wait_on(s, record_event(main_stream()));   // everything already queued on the main stream comes first
+        for (Track* t : writes) {
+            if (t->ready && t->home != run) wait_on(run, t->ready);
+            for (auto& b : t->busy) wait_on(run, b);      // readers on other lanes must be done before the overwrite
+            t->busy.clear();
+        }
+        for (Track* t : reads) if (t->ready && t->home != run) wait_on(run, t->ready);
+        set_current_stream(s);
+    }
+    void done(std::initializer_list<Track*> outs) {
+        if (s) {
+            EvRef e = record_event(s);
+            g_tail[lane_index(s)] = e;
+            for (Track* t : writes) { t->ready = e; t->home = s; }
+            for (Track* t : outs) { t->ready = e; t->home = s; t->busy.clear(); }
+            for (Track* t : reads) {
+                bool written = false;
+                for (Track* w : writes) if (w == t) written = true;
+                if (written || t->home == s) continue;    // same lane: stream order is enough
+                if (t->busy.size() >= 8) prune(t->busy);
+                t->busy.push_back(e);
+            }
+        } else {
+            for (Track* t : writes) { t->ready.reset(); t->home = nullptr; }
+            for (Track* t : outs) { t->ready.reset(); t->home = nullptr; t->busy.clear(); }
+        }
+        set_current_stream(nullptr);
+    }
+};
+// new ciphertext from f() reading the given handles
+template <class F> int op_new(bool heavy, std::initializer_list<Track*> reads, F&& f) {
+    Op op(heavy, {}, reads);
+    std::unique_ptr<Ciphertext> o = f();
+    op.done({&o->trk});
+    return push_ct(std::move(o));
+}
+// f() overwrites the handle `w` (and reads the others)
+template <class F> void op_inplace(bool heavy, Track* w, std::initializer_list<Track*> reads, F&& f) {
+    Op op(heavy, {w}, reads);
+    f();
+    op.done({});
+}
+// run f() where the handle lives and leave the host synchronised with it (Decrypt, Export*)
+template <class F> void op_host(Track* t, F&& f) {
+    Op op(false, {}, {t});
+    f();
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    op.done({});
+}
+// free a tracked buffer without making the main stream wait: the free is queued where the buffer lives, behind its readers
+template <class T> void release_tracked(HandleTable<T>& tab, int id) {
+    auto it = tab.live.find(id);
+    if (it == tab.live.end()) return;
+    Track& t = it->second->trk;
+    if (t.ready || !t.busy.empty()) {
+        cudaStream_t s = t.home ? t.home : lane(NLANES - 1);
+        for (auto& b : t.busy) wait_on(s, b);
+        set_current_stream(s);
+        tab.del(id);
+        set_current_stream(nullptr);
+    } else {
+        tab.del(id);
+    }
+}
+void settle_all() {                                       // before shared device state is torn down or rebuilt
+    cudaDeviceSynchronize();
+    for (int k = 0; k < NLANES; ++k) g_tail[k].reset();
+}
 }  // namespace
 
 extern "C" {
@@ -53,19 +184,21 @@ void NewScheme(int logN, int* logQ, int lenQ, int* logP, int lenP, int logScale,
     p.conjugate_invariant = (rt != "standard");
     u64 seed = g_seed;
     if (!g_seed_set) { std::random_device rd; seed = ((u64)rd() << 32) ^ rd(); }   // OS randomness, as Lattigo does
+    settle_all();
     lt_reset(); poly_reset(); boot_reset();
     g_scheme.reset();
     g_scheme = std::make_unique<Scheme>(p, seed);
 }
 void DeleteScheme(void) {
+    settle_all();
     lt_reset(); poly_reset(); boot_reset();
     g_scheme.reset();
 }
 void FreeCArray(void* p) { std::free(p); }
 
 // ---------------------------------------------------------------- tensors
-void DeletePlaintext(int id) { S().pts.del(id); }
-void DeleteCiphertext(int id) { S().cts.del(id); }
+void DeletePlaintext(int id) { release_tracked(S().pts, id); }
+void DeleteCiphertext(int id) { release_tracked(S().cts, id); }
 unsigned long GetPlaintextScale(int id) { return (unsigned long)PT(id).scale; }
 unsigned long GetCiphertextScale(int id) { return (unsigned long)CT(id).scale; }
 void SetPlaintextScale(int id, unsigned long scale) { PT(id).scale = (scale_t)scale; }
@@ -114,53 +247,65 @@ int Encode(float* values, int lenValues, int level, unsigned long scale) {
     return push_pt(s.encode(v.data(), lenValues, level, (scale_t)scale, s.log_max_slots));
 }
 ArrayResultFloat Decode(int ptID) {
-    std::vector<double2> v = S().decode(PT(ptID));
+    std::vector<double2> v = S().decode(PT(ptID));          // plaintexts are always settled: created synchronously or on the main stream
     std::vector<float> out(1 << S().log_max_slots, 0.0f);
     for (size_t i = 0; i < v.size() && i < out.size(); ++i) out[i] = (float)v[i].x;
     return make_array<float, ArrayResultFloat>(out);
 }
 void NewEncryptor(void) { S(); }
 void NewDecryptor(void) { S(); }
-int Encrypt(int ptID) { return push_ct(S().encrypt(PT(ptID))); }
-int Decrypt(int ctID) { return push_pt(S().decrypt(CT(ctID))); }
+int Encrypt(int ptID) { return op_new(false, {&PT(ptID).trk}, [&] { return S().encrypt(PT(ptID)); }); }
+int Decrypt(int ctID) {
+    std::unique_ptr<Plaintext> p;
+    op_host(&CT(ctID).trk, [&] { p = S().decrypt(CT(ctID)); });
+    return push_pt(std::move(p));
+}
 
 // ---------------------------------------------------------------- evaluator
 void B200_NoteEvaluatorKey(uint64_t g);
-void AddRotationKey(int rot) { u64 g = S().ctx->galois_element(rot); B200_NoteEvaluatorKey(g); S().galois_key(g); }
+void AddRotationKey(int rot) {
+    u64 g = S().ctx->galois_element(rot); B200_NoteEvaluatorKey(g);
+    if (!S().has_galois_key(g)) { S().galois_key(g); OB_CUDA(cudaStreamSynchronize(stream())); }   // shared by every lane from now on
+}
 void NewEvaluator(void) {
     Scheme& s = S();
     if (!s.has_sk()) return;
     for (int i = 1; i < (1 << s.log_max_slots); i *= 2) AddRotationKey(i);                        // LG/evaluator.go:25-31
 }
-int Negate(int ct) { auto o = fresh(); S().mul_int(CT(ct), -1, *o); return push_ct(std::move(o)); }
-int Rotate(int ct, int rot) { AddRotationKey(rot); S().rotate(CT(ct), rot, CT(ct)); return ct; }
-int RotateNew(int ct, int rot) { AddRotationKey(rot); auto o = fresh(); S().rotate(CT(ct), rot, *o); return push_ct(std::move(o)); }
-int Rescale(int ct) { S().rescale(CT(ct), CT(ct)); return ct; }
-int RescaleNew(int ct) { S().rescale(CT(ct), CT(ct)); return push_ct(S().clone(CT(ct))); }   // LG/evaluator.go:91-99: rescales the input too
-int AddScalar(int ct, float c) { S().add_const(CT(ct), (double)c, CT(ct)); return ct; }
-int AddScalarNew(int ct, float c) { auto o = fresh(); S().add_const(CT(ct), (double)c, *o); return push_ct(std::move(o)); }
-int SubScalar(int ct, float c) { S().add_const(CT(ct), -(double)c, CT(ct)); return ct; }
-int SubScalarNew(int ct, float c) { auto o = fresh(); S().add_const(CT(ct), -(double)c, *o); return push_ct(std::move(o)); }
-int MulScalarInt(int ct, int k) { S().mul_int(CT(ct), k, CT(ct)); return ct; }
-int MulScalarIntNew(int ct, int k) { auto o = fresh(); S().mul_int(CT(ct), k, *o); return push_ct(std::move(o)); }
-int MulScalarFloat(int ct, float c) { S().mul_float(CT(ct), (double)c, CT(ct)); return ct; }
-int MulScalarFloatNew(int ct, float c) { auto o = fresh(); S().mul_float(CT(ct), (double)c, *o); return push_ct(std::move(o)); }
-int AddPlaintext(int ct, int pt) { S().add_pt(CT(ct), PT(pt), CT(ct), false); return ct; }
-int AddPlaintextNew(int ct, int pt) { auto o = fresh(); S().add_pt(CT(ct), PT(pt), *o, false); return push_ct(std::move(o)); }
-int SubPlaintext(int ct, int pt) { S().add_pt(CT(ct), PT(pt), CT(ct), true); return ct; }
-int SubPlaintextNew(int ct, int pt) { auto o = fresh(); S().add_pt(CT(ct), PT(pt), *o, true); return push_ct(std::move(o)); }
-int MulPlaintext(int ct, int pt) { S().mul_pt(CT(ct), PT(pt), CT(ct)); return ct; }
-int MulPlaintextNew(int ct, int pt) { auto o = fresh(); S().mul_pt(CT(ct), PT(pt), *o); return push_ct(std::move(o)); }
-int AddCiphertext(int a, int b) { S().add_ct(CT(a), CT(b), CT(a), false); return a; }
-int AddCiphertextNew(int a, int b) { auto o = fresh(); S().add_ct(CT(a), CT(b), *o, false); return push_ct(std::move(o)); }
-int SubCiphertext(int a, int b) { S().add_ct(CT(a), CT(b), CT(a), true); return a; }
-int SubCiphertextNew(int a, int b) { auto o = fresh(); S().add_ct(CT(a), CT(b), *o, true); return push_ct(std::move(o)); }
-int MulRelinCiphertext(int a, int b) { S().mul_relin(CT(a), CT(b), CT(a)); return a; }
-int MulRelinCiphertextNew(int a, int b) { auto o = fresh(); S().mul_relin(CT(a), CT(b), *o); return push_ct(std::move(o)); }
+#define TRK(id) (&CT(id).trk)
+#define PTRK(id) (&PT(id).trk)
+int Negate(int ct) { return op_new(false, {TRK(ct)}, [&] { auto o = fresh(); S().mul_int(CT(ct), -1, *o); return o; }); }
+int Rotate(int ct, int rot) { AddRotationKey(rot); op_inplace(true, TRK(ct), {}, [&] { S().rotate(CT(ct), rot, CT(ct)); }); return ct; }
+int RotateNew(int ct, int rot) { AddRotationKey(rot); return op_new(true, {TRK(ct)}, [&] { auto o = fresh(); S().rotate(CT(ct), rot, *o); return o; }); }
+int Rescale(int ct) { op_inplace(false, TRK(ct), {}, [&] { S().rescale(CT(ct), CT(ct)); }); return ct; }
+int RescaleNew(int ct) {                                                                    // LG/evaluator.go:91-99: rescales the input too
+    op_inplace(false, TRK(ct), {}, [&] { S().rescale(CT(ct), CT(ct)); });
+    return op_new(false, {TRK(ct)}, [&] { return S().clone(CT(ct)); });
+}
+int AddScalar(int ct, float c) { op_inplace(false, TRK(ct), {}, [&] { S().add_const(CT(ct), (double)c, CT(ct)); }); return ct; }
+int AddScalarNew(int ct, float c) { return op_new(false, {TRK(ct)}, [&] { auto o = fresh(); S().add_const(CT(ct), (double)c, *o); return o; }); }
+int SubScalar(int ct, float c) { op_inplace(false, TRK(ct), {}, [&] { S().add_const(CT(ct), -(double)c, CT(ct)); }); return ct; }
+int SubScalarNew(int ct, float c) { return op_new(false, {TRK(ct)}, [&] { auto o = fresh(); S().add_const(CT(ct), -(double)c, *o); return o; }); }
+int MulScalarInt(int ct, int k) { op_inplace(false, TRK(ct), {}, [&] { S().mul_int(CT(ct), k, CT(ct)); }); return ct; }
+int MulScalarIntNew(int ct, int k) { return op_new(false, {TRK(ct)}, [&] { auto o = fresh(); S().mul_int(CT(ct), k, *o); return o; }); }
+int MulScalarFloat(int ct, float c) { op_inplace(false, TRK(ct), {}, [&] { S().mul_float(CT(ct), (double)c, CT(ct)); }); return ct; }
+int MulScalarFloatNew(int ct, float c) { return op_new(false, {TRK(ct)}, [&] { auto o = fresh(); S().mul_float(CT(ct), (double)c, *o); return o; }); }
+int AddPlaintext(int ct, int pt) { op_inplace(false, TRK(ct), {PTRK(pt)}, [&] { S().add_pt(CT(ct), PT(pt), CT(ct), false); }); return ct; }
+int AddPlaintextNew(int ct, int pt) { return op_new(false, {TRK(ct), PTRK(pt)}, [&] { auto o = fresh(); S().add_pt(CT(ct), PT(pt), *o, false); return o; }); }
+int SubPlaintext(int ct, int pt) { op_inplace(false, TRK(ct), {PTRK(pt)}, [&] { S().add_pt(CT(ct), PT(pt), CT(ct), true); }); return ct; }
+int SubPlaintextNew(int ct, int pt) { return op_new(false, {TRK(ct), PTRK(pt)}, [&] { auto o = fresh(); S().add_pt(CT(ct), PT(pt), *o, true); return o; }); }
+int MulPlaintext(int ct, int pt) { op_inplace(false, TRK(ct), {PTRK(pt)}, [&] { S().mul_pt(CT(ct), PT(pt), CT(ct)); }); return ct; }
+int MulPlaintextNew(int ct, int pt) { return op_new(false, {TRK(ct), PTRK(pt)}, [&] { auto o = fresh(); S().mul_pt(CT(ct), PT(pt), *o); return o; }); }
+int AddCiphertext(int a, int b) { op_inplace(false, TRK(a), {TRK(b)}, [&] { S().add_ct(CT(a), CT(b), CT(a), false); }); return a; }
+int AddCiphertextNew(int a, int b) { return op_new(false, {TRK(a), TRK(b)}, [&] { auto o = fresh(); S().add_ct(CT(a), CT(b), *o, false); return o; }); }
+int SubCiphertext(int a, int b) { op_inplace(false, TRK(a), {TRK(b)}, [&] { S().add_ct(CT(a), CT(b), CT(a), true); }); return a; }
+int SubCiphertextNew(int a, int b) { return op_new(false, {TRK(a), TRK(b)}, [&] { auto o = fresh(); S().add_ct(CT(a), CT(b), *o, true); return o; }); }
+int MulRelinCiphertext(int a, int b) { op_inplace(true, TRK(a), {TRK(b)}, [&] { S().mul_relin(CT(a), CT(b), CT(a)); }); return a; }
+int MulRelinCiphertextNew(int a, int b) { return op_new(true, {TRK(a), TRK(b)}, [&] { auto o = fresh(); S().mul_relin(CT(a), CT(b), *o); return o; }); }
 
 // ---------------------------------------------------------------- extras required by the (drifted) Python layer
-int CloneCiphertext(int ct) { return push_ct(S().clone(CT(ct))); }                    // PY/tensors.py:229
-int ModDropCiphertext(int ct) { Ciphertext& c = CT(ct); OB_CHECK(c.level >= 1, "mod drop at level 0"); S().drop_level(c, c.level - 1); return ct; }  // PY/evaluator.py:36-40
+int CloneCiphertext(int ct) { return op_new(false, {TRK(ct)}, [&] { return S().clone(CT(ct)); }); }                    // PY/tensors.py:229
+int ModDropCiphertext(int ct) { Ciphertext& c = CT(ct); OB_CHECK(c.level >= 1, "mod drop at level 0"); op_inplace(false, TRK(ct), {}, [&] { S().drop_level(c, c.level - 1); }); return ct; }  // PY/evaluator.py:36-40
 
 // ---------------------------------------------------------------- interop: raw limbs in / out (parity tests, e2e bench, multi-GPU gather)
 int B200_ImportCiphertext(const uint64_t* data, int level, int degree, double scale, int logSlots) {
@@ -172,10 +317,15 @@ int B200_ImportCiphertext(const uint64_t* data, int level, int degree, double sc
 }
 void B200_ExportCiphertext(int ct, uint64_t* out) {
     Ciphertext& c = CT(ct);
-    OB_CUDA(cudaMemcpyAsync(out, c.data.p, (size_t)(c.degree + 1) * (c.level + 1) * S().N * 8, cudaMemcpyDeviceToHost, stream()));
-    OB_CUDA(cudaStreamSynchronize(stream()));
+    op_host(&c.trk, [&] {
+        OB_CUDA(cudaMemcpyAsync(out, c.data.p, (size_t)(c.degree + 1) * (c.level + 1) * S().N * 8, cudaMemcpyDeviceToHost, stream()));
+    });
 }
-void* B200_CiphertextDevicePtr(int ct) { return CT(ct).data.p; }
+void* B200_CiphertextDevicePtr(int ct) {                  // the caller touches the buffer from its own streams: settle it first
+    Ciphertext& c = CT(ct);
+    if (c.trk.ready || !c.trk.busy.empty()) { OB_CUDA(cudaDeviceSynchronize()); c.trk = Track(); }
+    return c.data.p;
+}
 double B200_GetCiphertextScaleF64(int ct) { return (double)CT(ct).scale; }
 void B200_SetCiphertextScaleF64(int ct, double s) { CT(ct).scale = (scale_t)s; }
 void B200_ExportPlaintext(int pt, uint64_t* out) {
@@ -224,7 +374,7 @@ void B200_DecodeF64(int pt, double* out_re, double* out_im) {
     std::vector<double2> v = S().decode(PT(pt));
     for (size_t i = 0; i < v.size(); ++i) { out_re[i] = v[i].x; if (out_im) out_im[i] = v[i].y; }
 }
-int B200_Conjugate(int ct) { auto o = fresh(); S().conjugate(CT(ct), *o); return push_ct(std::move(o)); }
+int B200_Conjugate(int ct) { return op_new(true, {TRK(ct)}, [&] { auto o = fresh(); S().conjugate(CT(ct), *o); return o; }); }
 
 }  // extern "C"
 
@@ -252,8 +402,8 @@ int GenerateLinearTransform(int* diagIdx, int nIdx, float* diagData, int nData, 
     (void)ioMode;   // "load" is served by LoadPlaintextDiagonal overwriting the encoded diagonals
     return lt_push(lt_build(s, diags, level, s.q_at(level), s.log_max_slots, log_ratio));
 }
-int EvaluateLinearTransform(int transform, int ct) { return push_ct(lt_apply(S(), lt_get(transform), CT(ct))); }
-void DeleteLinearTransform(int id) { lt_delete(id); }
+int EvaluateLinearTransform(int transform, int ct) { return op_new(true, {&CT(ct).trk}, [&] { return lt_apply(S(), lt_get(transform), CT(ct)); }); }
+void DeleteLinearTransform(int id) { settle_all(); lt_delete(id); }
 ArrayResultInt GetLinearTransformRotationKeys(int transform) {
     return make_array<u64, ArrayResultInt>(lt_galois_elements(S(), lt_get(transform)));
 }
@@ -315,10 +465,10 @@ void LoadPlaintextDiagonal(unsigned char* data, unsigned long len, int transform
     OB_CUDA(cudaMemcpyAsync(lt.diags.u() + (size_t)it->second * lt.W * s.N, data + 16, bytes, cudaMemcpyHostToDevice, stream()));
     OB_CUDA(cudaStreamSynchronize(stream()));
 }
-void RemovePlaintextDiagonals(int transform) { lt_get(transform).diags.release(); }
+void RemovePlaintextDiagonals(int transform) { settle_all(); lt_get(transform).diags.release(); }
 void RemoveRotationKeys(void) {
     Scheme& s = S();
-    OB_CUDA(cudaStreamSynchronize(stream()));
+    settle_all();
     for (u64 g : g_lt_keys) if (!g_eval_keys.count(g)) s.galois_keys.erase(g);
     g_lt_keys.clear();
 }
@@ -346,12 +496,12 @@ int B200_GeneratePolynomialF64(const double* coeffs, int n, int chebyshev) {
     return poly_push(std::move(p));
 }
 int EvaluatePolynomial(int ct, int poly, unsigned long outScale) {
-    return push_ct(poly_evaluate(S(), CT(ct), poly_get(poly), (scale_t)outScale));
+    return op_new(true, {&CT(ct).trk}, [&] { return poly_evaluate(S(), CT(ct), poly_get(poly), (scale_t)outScale); });
 }
 int GetPolyDepth(int poly) { return poly_depth(poly_get(poly)); }
 
 // ---------------------------------------------------------------- bootstrapping (LG/bootstrapper.go:19-93)
 void NewBootstrapper(int* logPs, int n, int numSlots) { boot_new(S(), std::vector<int>(logPs, logPs + n), numSlots); }
-int Bootstrap(int ct, int numSlots) { return push_ct(boot_apply(S(), CT(ct), numSlots)); }
-void DeleteBootstrappers(void) { boot_reset(); }
+int Bootstrap(int ct, int numSlots) { return op_new(true, {&CT(ct).trk}, [&] { return boot_apply(S(), CT(ct), numSlots); }); }
+void DeleteBootstrappers(void) { settle_all(); boot_reset(); }
 }  // extern "C"

@@ -55,7 +55,7 @@ void B200_DeleteContext(void* h) {
 }
 uint64_t B200_ContextPsi(void* h, int idx) { return R(h)->ctx->psi[idx]; }
 
-void B200_Sync(void) { OB_CUDA(cudaStreamSynchronize(stream())); }
+void B200_Sync(void) { ensure_device(); OB_CUDA(cudaDeviceSynchronize()); }        // main stream, dataflow lanes and side streams
 unsigned long long B200_LaunchCount(void) { return g_launches; }
 void* B200_Stream(void) { return (void*)stream(); }
 void B200_TimerStart(void) {
@@ -63,6 +63,7 @@ void B200_TimerStart(void) {
     OB_CUDA(cudaEventRecord(g_ev0, stream()));
 }
 float B200_TimerStopMs(void) {
+    OB_CUDA(cudaDeviceSynchronize());                        // work on the dataflow lanes (capi.cu) counts too
     OB_CUDA(cudaEventRecord(g_ev1, stream()));
     OB_CUDA(cudaEventSynchronize(g_ev1));
     float ms = 0; OB_CUDA(cudaEventElapsedTime(&ms, g_ev0, g_ev1));

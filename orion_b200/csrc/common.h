@@ -59,6 +59,19 @@ inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 #endif
 
 cudaStream_t stream();          // the stream work is currently issued on (the library's main stream unless forked)
+cudaStream_t main_stream();
+void set_current_stream(cudaStream_t s);     // nullptr = back to the main stream
+// Pooled CUDA event (timing disabled) with shared ownership: ciphertext handles keep the event of their last writer and of
+// readers on other streams (dataflow lanes, capi.cu); the event returns to the pool when the last holder drops it.
+struct DevEvent {
+    cudaEvent_t e = nullptr;
+    DevEvent();
+    ~DevEvent();
+    DevEvent(const DevEvent&) = delete;
+    DevEvent& operator=(const DevEvent&) = delete;
+};
+typedef std::shared_ptr<DevEvent> EvRef;
+EvRef record_event(cudaStream_t s);          // a fresh pooled event recorded on s
 
 // Fork / join over side streams: independent sub-computations (the two EvalMod halves of a bootstrap, the independent
 // products of a polynomial evaluation) are issued on side streams so their launch-latency-bound kernel chains overlap

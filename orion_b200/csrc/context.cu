@@ -10,6 +10,7 @@ static bool g_dev_ok = false;
 
 void ensure_device() {
     if (g_dev_ok) return;
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);      // lanes + side streams: no channel sharing (no effect once a context exists)
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0)
@@ -23,17 +24,32 @@ void ensure_device() {
     OB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
     uint64_t thr = UINT64_MAX;
     OB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    // lanes and side streams share this pool: never let an allocation on one stream wait for a free queued on another
+    // (that would serialise independent lanes); reuse across streams only once the free is known to have completed
+    int off = 0;
+    if (const char* e = std::getenv("ORION_B200_POOL_DEPS")) off = std::atoi(e);
+    OB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolReuseAllowInternalDependencies, &off));
     g_dev_ok = true;
 }
 static cudaStream_t g_cur = nullptr;                      // current stream while forked (single host thread by contract)
 cudaStream_t stream() { ensure_device(); return g_cur ? g_cur : g_stream; }
 
 // ---- fork / join ----
-static std::vector<cudaStream_t> g_side_pool;             // free side streams
-static std::vector<cudaEvent_t> g_event_pool;
+static std::vector<cudaStream_t>& g_side_pool = *new std::vector<cudaStream_t>();   // free side streams (leaked, like every global owner)
+static bool g_side_pool_init = false;
+static std::vector<cudaEvent_t>& g_event_pool = *new std::vector<cudaEvent_t>();
 static cudaEvent_t take_event() {
     if (g_event_pool.empty()) { cudaEvent_t e; OB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); return e; }
     cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e;
+}
+cudaStream_t main_stream() { ensure_device(); return g_stream; }
+void set_current_stream(cudaStream_t s) { g_cur = (s == g_stream) ? nullptr : s; }
+DevEvent::DevEvent() : e(take_event()) {}
+DevEvent::~DevEvent() { if (e) g_event_pool.push_back(e); }      // waits already enqueued keep the state they captured
+EvRef record_event(cudaStream_t s) {
+    EvRef r = std::make_shared<DevEvent>();
+    OB_CUDA(cudaEventRecord(r->e, s));
+    return r;
 }
 // PDL policy: measured +3 % on the logN=16 key switch (tail of one kernel overlaps the head of the next) and -30 % on a
 // bare rescale chain, but -9 % on the ResNet-20 replay at logN=13, where early-resident dependents take SM slots from
@@ -89,8 +105,12 @@ StreamFork::StreamFork(int n) : parent_(stream()) {
     OB_CUDA(cudaEventRecord(e, parent_));
     for (int i = 0; i < n; ++i) {
         cudaStream_t s;
+        if (!g_side_pool_init) {                              // pre-created, handed out FIFO: forks of operations that run
+            g_side_pool_init = true;                          // concurrently on different lanes get different side streams
+            for (int k = 0; k < 16; ++k) { cudaStream_t t; OB_CUDA(cudaStreamCreateWithFlags(&t, cudaStreamNonBlocking)); g_side_pool.push_back(t); }
+        }
         if (g_side_pool.empty()) OB_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
-        else { s = g_side_pool.back(); g_side_pool.pop_back(); }
+        else { s = g_side_pool.front(); g_side_pool.erase(g_side_pool.begin()); }
         OB_CUDA(cudaStreamWaitEvent(s, e, 0));
         side_.push_back(s);
     }

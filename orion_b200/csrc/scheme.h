@@ -9,15 +9,24 @@ namespace ob {
 
 typedef long double scale_t;    // 64-bit mantissa: holds every uint64 scale of the C ABI exactly
 
+// Dataflow tracking of a handle's device buffer (capi.cu lanes): the stream and event of its last writer, and the events
+// of readers that ran on other streams (a later writer / the free must wait for them).  Empty = settled on the main stream.
+struct Track {
+    cudaStream_t home = nullptr;
+    EvRef ready;
+    std::vector<EvRef> busy;
+};
 struct Plaintext {
     DevBuf data;                // [level+1][N], NTT domain
     int level = 0, log_slots = 0;
     scale_t scale = 1;
+    Track trk;
 };
 struct Ciphertext {
     DevBuf data;                // [degree+1][level+1][N], NTT domain
     int level = 0, degree = 1, log_slots = 0;
     scale_t scale = 1;
+    Track trk;
     u64* poly(int p, int N) const { return data.u() + (size_t)p * (level + 1) * N; }
 };
 struct EvalKey { DevBuf data; };   // [beta(max level)][2][nQ+nP][N], NTT domain, Montgomery form

@@ -82,3 +82,36 @@ def test_mlp_reference_test_config_conjugate_invariant(b200lib):
     mae = float(np.mean(np.abs(clear - fhe)))
     assert mae < 0.0075, (mae, clear, fhe)
     assert int(np.argmax(fhe)) == int(np.argmax(clear))
+
+
+def _replay_in_subprocess(name, env_extra):
+    """Run one trace replay in a fresh process (the lane switch is read once per process) and return its decoded output."""
+    import json
+    import subprocess
+    import sys
+    code = (
+        "import os, sys, json, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "from orion_b200.bindings import B200Library\n"
+        "from orion_b200.replay import replay_model\n"
+        "B = B200Library(); B.B200_SetSeed(42)\n"
+        "res = replay_model(B, %r, %r)\n"
+        "print('OUT' + json.dumps([float(v).hex() for v in np.asarray(res['output'])[:64]]))\n"
+    ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.join(GOLD, "trace_%s.json" % name),
+         os.path.join(GOLD, "trace_%s.npz" % name))
+    env = dict(os.environ); env.update(env_extra)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("OUT")][-1]
+    return json.loads(line[3:])
+
+
+@pytest.mark.parametrize("name", ["resnet20", "lola"])
+def test_dataflow_lanes_give_the_single_stream_result(b200lib, name):
+    """The lane scheduler of the C ABI (csrc/capi.cu: independent ciphertexts on different streams, events per handle)
+    must not change a single bit: the decoded logits of a whole inference with lanes on equal those with
+    ORION_B200_ASYNC=0 (everything on one stream) exactly.  ResNet-20 is the trace with 4 ciphertexts per tensor."""
+    a = _replay_in_subprocess(name, {"ORION_B200_ASYNC": "1"})
+    b = _replay_in_subprocess(name, {"ORION_B200_ASYNC": "0"})
+    c = _replay_in_subprocess(name, {"ORION_B200_ASYNC": "1", "ORION_B200_STREAMS": "0"})
+    assert a == b == c

@@ -37,3 +37,20 @@ if "--by-op" in sys.argv:
     for k, v in tsum.most_common(14):
         print("%-26s n=%4d  %8.1f ms  %5.1f%%  %7d launches  (%.1f us/launch)" % (k, cnt[k], v * 1e3, 100 * v / tot, lsum[k], 1e6 * v / max(1, lsum[k])))
     print("total %.3f s" % tot)
+
+if "--host-time" in sys.argv:
+    # host-side enqueue time per op type (no synchronisation added): how far the launch rate is from the GPU time
+    import collections
+    tsum, cnt = collections.Counter(), collections.Counter()
+    orig = r._run
+    def timed(i, op):
+        t0 = time.perf_counter()
+        orig(i, op)
+        tsum[op[0]] += time.perf_counter() - t0; cnt[op[0]] += 1
+    r._run = timed
+    lib.B200_Sync(); t0 = time.perf_counter()
+    r.infer(); lib.B200_Sync()
+    wall = time.perf_counter() - t0
+    for k, v in tsum.most_common(8):
+        print("host %-26s n=%4d  %8.1f ms" % (k, cnt[k], v * 1e3))
+    print("host total %.3f s of wall %.3f s (Decrypt/Decode include the final synchronisation)" % (sum(tsum.values()), wall))
