@@ -41,17 +41,23 @@ ew_binary_kernel(const u64* __restrict__ a, int a_stride, const u64* __restrict_
     *(ulonglong2*)(out + ((size_t)p * out_stride + t) * N + x) = r;
 }
 
-// MODE 0: out = a * s (Shoup);  MODE 1: out = a + s (only on poly `only_poly`, copy elsewhere)
+// MODE 0: out = a * s (Shoup);  MODE 1: out = a + s (only on poly `only_poly`, copy elsewhere).
+// The per-limb scalars travel BY VALUE in the kernel parameters (up to 96 limbs = 1.5 KB of the 4 KB parameter space):
+// no staging copy and no allocation per call -- at logN = 13 a polynomial evaluation issues thousands of these and the
+// pageable copy was a visible share of the host-side enqueue time.
+constexpr int SCAL_MAX = 96;
+struct ScalarTab { ulonglong2 v[SCAL_MAX]; };
 template <int MODE>
 __global__ void __launch_bounds__(TPB)
 ew_scalar_kernel(const u64* __restrict__ a, int a_stride, u64* __restrict__ out, int out_stride, int L, int nQ, int N,
-                 const ModConst* __restrict__ mc, const ulonglong2* __restrict__ scal, int only_poly) {
+                 const ModConst* __restrict__ mc, const __grid_constant__ ScalarTab tab, const ulonglong2* __restrict__ scal,
+                 int only_poly) {
     OB_PDL_SYNC();
     const int t = blockIdx.y, p = blockIdx.z;
     const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
     if (x >= N) return;
     const u64 q = mc[chain_of(t, L, nQ)].q;
-    const ulonglong2 s = scal[t];
+    const ulonglong2 s = scal ? scal[t] : tab.v[t];
     ulonglong2 v = *(const ulonglong2*)(a + ((size_t)p * a_stride + t) * N + x);
     if (MODE == 0) { v.x = shoup_mul(v.x, s.x, s.y, q); v.y = shoup_mul(v.y, s.x, s.y, q); }
     else if (p == only_poly) { v.x = add_mod(v.x, s.x, q); v.y = add_mod(v.y, s.x, q); }
@@ -113,30 +119,34 @@ void ew_binary(Context& c, EwOp op, const u64* a, int a_stride, const u64* b, in
 #undef OB_EW
 }
 
-static const ulonglong2* upload_scalars(Context& c, int limbs, int L, const std::vector<u64>& scalars, DevBuf& buf) {
-    std::vector<ulonglong2> h(limbs);
+// scalars -> (value, Shoup companion) per limb, in the parameter table when they fit, else in a device buffer
+static const ulonglong2* stage_scalars(Context& c, int limbs, int L, const std::vector<u64>& scalars, ScalarTab& tab, DevBuf& buf) {
+    std::vector<ulonglong2> big;
+    ulonglong2* h = tab.v;
+    if (limbs > SCAL_MAX) { big.resize(limbs); h = big.data(); }
     for (int t = 0; t < limbs; ++t) {
         u64 q = c.mod[t < L ? t : c.nQ + (t - L)];
         u64 s = scalars[t] % q;
         h[t] = make_ulonglong2(s, shoup_companion(s, q));
     }
+    if (limbs <= SCAL_MAX) return nullptr;
     buf.alloc(limbs * sizeof(ulonglong2));
-    // small pageable copy: the driver stages it, so the host vector may die after the call
-    OB_CUDA(cudaMemcpyAsync(buf.p, h.data(), limbs * sizeof(ulonglong2), cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaMemcpyAsync(buf.p, h, limbs * sizeof(ulonglong2), cudaMemcpyHostToDevice, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));               // `big` dies at return
     return buf.as<ulonglong2>();
 }
 
 void ew_mul_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_stride, int polys, int limbs, int L,
                    const std::vector<u64>& scalars) {
-    DevBuf buf; const ulonglong2* s = upload_scalars(c, limbs, L, scalars, buf);
+    ScalarTab tab; DevBuf buf; const ulonglong2* s = stage_scalars(c, limbs, L, scalars, tab, buf);
     dim3 grid(c.N / (2 * TPB), limbs, polys);
-    OB_LAUNCH((ew_scalar_kernel<0>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), s, 0);
+    OB_LAUNCH((ew_scalar_kernel<0>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), tab, s, 0);
 }
 void ew_add_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_stride, int polys, int limbs, int L,
                    const std::vector<u64>& scalars, int only_poly) {
-    DevBuf buf; const ulonglong2* s = upload_scalars(c, limbs, L, scalars, buf);
+    ScalarTab tab; DevBuf buf; const ulonglong2* s = stage_scalars(c, limbs, L, scalars, tab, buf);
     dim3 grid(c.N / (2 * TPB), limbs, polys);
-    OB_LAUNCH((ew_scalar_kernel<1>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), s, only_poly);
+    OB_LAUNCH((ew_scalar_kernel<1>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), tab, s, only_poly);
 }
 
 void tensor_product(Context& c, const u64* a, int a_stride, const u64* b, int b_stride, u64* out, int L) {
