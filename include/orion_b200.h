@@ -47,6 +47,7 @@ float    B200_TimerStopMs(void);
 /* Kernel probe: while enabled, every launch of the key switch's dominant kernel (fused second NTT pass + evaluation-key
  * inner product, FP64-path limbs) is bracketed by CUDA events on its own stream; ReadMs returns the summed kernel time
  * and the launch count since the last read.  Measurement aid for bench.py's roofline object. */
+void     B200_HostProfDump(void);                            /* ORION_B200_HOSTPROF=1: print and reset the host-side enqueue timers */
 void     B200_ProbeEnable(int on);
 double   B200_ProbeReadMs(long* launches);
 void*    B200_DevAlloc(size_t words);

@@ -212,6 +212,7 @@ void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
 }
 
 std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_slots) {
+    OB_HP("boot_apply (total)");
     auto it = g_boot.find(num_slots);
     OB_CHECK(it != g_boot.end(), "Bootstrap: no bootstrapper for this slot count (call NewBootstrapper)");
     OB_CHECK(in.degree == 1, "Bootstrap expects a degree-1 ciphertext");

@@ -69,6 +69,7 @@ float B200_TimerStopMs(void) {
     float ms = 0; OB_CUDA(cudaEventElapsedTime(&ms, g_ev0, g_ev1));
     return ms;
 }
+void B200_HostProfDump(void) { hostprof_dump(); }
 void B200_ProbeEnable(int on) { probe_enable(on != 0); }
 double B200_ProbeReadMs(long* launches) { return probe_read_ms(launches); }
 

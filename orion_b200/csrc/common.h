@@ -38,6 +38,13 @@ void probe_enable(bool on);
 void probe_begin();
 void probe_end();
 double probe_read_ms(long* launches);
+// Host-side enqueue profiler (ORION_B200_HOSTPROF=1): scoped wall-clock timers around the host work of the hot path
+// (launch API, allocator, plan lookups, events); B200_HostProfDump prints the table.  Off: one predictable branch.
+struct HostProf { int id; unsigned long long t0; explicit HostProf(int i); ~HostProf(); };
+int hostprof_slot(const char* name);
+bool hostprof_on();
+void hostprof_dump();
+#define OB_HP(name) static const int hp_slot__ = ::ob::hostprof_slot(name); ::ob::HostProf hp__(hp_slot__)
 bool dry_run();        // ORION_B200_DRYRUN=1: skip the launches (host-side enqueue cost measurement only; results are garbage)
 template <class... KArgs, class... Args>
 inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
@@ -48,6 +55,7 @@ inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    OB_HP("cudaLaunchKernelEx");
     OB_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
 }
 #define OB_LAUNCH(kernel, grid, block, smem, stream, ...) do { \

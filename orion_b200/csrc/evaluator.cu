@@ -69,6 +69,7 @@ const KsPlan& PolyEvaluator::ks_plan(int level) {
 }
 
 void PolyEvaluator::decompose(int level, const u64* c1_ntt, u64* digits) {
+    OB_HP("decompose (total)");
     const KsPlan& p = ks_plan(level);
     DevBuf coef((size_t)p.L * ctx.N * 8);
     ntt_inverse(ctx, c1_ntt, coef.u(), p.intt_c1);
@@ -83,6 +84,7 @@ void PolyEvaluator::moddown(int level, const u64* acc, int polys, const u64* add
 
 void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, const u64* addend, int addend_stride,
                               int addend_polys, u64* out, int out_stride, int addend_period, int addend_zstride) {
+    OB_HP("moddown_n (total)");
     OB_CHECK(n >= 1 && n <= 4096, "moddown_n: polynomial count out of range");
     const KsPlan& p = ks_plan(level);
     const size_t N = ctx.N;
@@ -164,6 +166,7 @@ static bool use_fused_ip(const Context& c, int W, int n) {
 
 void PolyEvaluator::keyswitch(int level, const u64* c1_ntt, const u64* evk, const u64* addend, int addend_stride,
                               int addend_polys, u64* out, int out_stride) {
+    OB_HP("keyswitch (total)");
     const KsPlan& p = ks_plan(level);
     DevBuf digits(digits_words(level) * 8), acc((size_t)2 * p.W * ctx.N * 8);
     decompose(level, c1_ntt, digits.u());
@@ -194,6 +197,7 @@ void PolyEvaluator::keyswitch_n(int level, int n, const u64* c1s, int c1_zstride
 }
 
 void PolyEvaluator::rescale(int level, const u64* in, int in_stride, u64* out, int out_stride, int polys) {
+    OB_HP("rescale (total)");
     OB_CHECK(level >= 1, "cannot rescale at level 0");
     OB_CHECK(polys >= 1 && polys <= 2, "rescale handles 1 or 2 polynomials");
     const size_t N = ctx.N;

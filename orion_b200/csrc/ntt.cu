@@ -487,6 +487,7 @@ ntt2_submul_kernel(const u64* __restrict__ a, int a_stride, const u64* __restric
 }  // namespace
 
 NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
+    OB_HP("make_ntt_plan");
     NttPlan p; p.n = (int)limbs.size();
     if (p.n == 0) return p;
     std::vector<LimbDesc> second = limbs;

@@ -190,6 +190,7 @@ void poly_reset() { g_polys.reset(); }
 int poly_depth(const Polynomial& p) { return bitlen(p.degree()); }
 
 std::unique_ptr<Ciphertext> poly_evaluate(Scheme& s, const Ciphertext& in, const Polynomial& poly, scale_t out_scale) {
+    OB_HP("poly_evaluate (total)");
     OB_CHECK(in.degree == 1, "EvaluatePolynomial expects a degree-1 ciphertext");
     const int d = poly.degree();
     OB_CHECK(d >= 1, "EvaluatePolynomial: degree must be at least 1");

@@ -8,6 +8,7 @@ namespace ob {
 
 // residues of (+/-) an integer-valued long double, one per limb of the QP-at-level layout
 std::vector<u64> const_to_rns(const Context& c, long double mag, bool neg, int limbs, int L) {
+    OB_HP("const_to_rns");
     std::vector<u64> r(limbs);
     for (int t = 0; t < limbs; ++t) {
         const u64 q = c.mod[t < L ? t : c.nQ + (t - L)];

@@ -28,6 +28,7 @@ RAW_SIGNATURES = {
     "B200_Stream": ([], c_vp),
     "B200_TimerStart": ([], None),
     "B200_TimerStopMs": ([], ctypes.c_float),
+    "B200_HostProfDump": ([], None),
     "B200_ProbeEnable": ([ctypes.c_int], None),
     "B200_ProbeReadMs": ([ctypes.POINTER(ctypes.c_long)], ctypes.c_double),
     "B200_DevAlloc": ([c_sz], c_vp),

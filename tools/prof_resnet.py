@@ -54,3 +54,10 @@ if "--host-time" in sys.argv:
     for k, v in tsum.most_common(8):
         print("host %-26s n=%4d  %8.1f ms" % (k, cnt[k], v * 1e3))
     print("host total %.3f s of wall %.3f s (Decrypt/Decode include the final synchronisation)" % (sum(tsum.values()), wall))
+
+if "--hostprof" in sys.argv:
+    # ORION_B200_HOSTPROF=1 python tools/prof_resnet.py 2 --hostprof : C++-side enqueue timers for one inference
+    lib.B200_Sync(); lib.B200_HostProfDump()
+    t0 = time.perf_counter(); r.infer(); lib.B200_Sync()
+    print("hostprof inference wall %.3f s" % (time.perf_counter() - t0), flush=True)
+    lib.B200_HostProfDump()
