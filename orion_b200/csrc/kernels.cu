@@ -64,6 +64,37 @@ ew_scalar_kernel(const u64* __restrict__ a, int a_stride, u64* __restrict__ out,
     *(ulonglong2*)(out + ((size_t)p * out_stride + t) * N + x) = v;
 }
 
+// out[p][t][x] = sum_i k_i[t] * src_i[p][t][x]  (+ c0[t] on polynomial 0): the leaves of the polynomial evaluator
+// (sum of constant multiples of power-basis ciphertexts) in ONE launch instead of a multiply, an add and, for
+// operands that sit at a higher level, a copy per term.  Operands are read in place with their own limb stride, so a
+// higher-level operand is "dropped" by simply not reading its upper limbs.  Residues travel in the kernel parameters.
+struct LinCombArgs {
+    const u64* src[LINCOMB_MAX];
+    int stride[LINCOMB_MAX];
+    u64 k[(LINCOMB_MAX + 1) * LINCOMB_LIMBS];             // [term][limb]; row n = additive constant
+};
+__global__ void __launch_bounds__(TPB)
+lincomb_kernel(const __grid_constant__ LinCombArgs a, int n, int has_c0, u64* __restrict__ out, int L, int N,
+               const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
+    const int t = blockIdx.y, p = blockIdx.z;
+    const int x = (blockIdx.x * TPB + threadIdx.x) * 2;
+    if (x >= N) return;
+    const ModConst m = mc[t];
+    ulonglong2 acc = make_ulonglong2(0, 0);
+    for (int i = 0; i < n; ++i) {
+        const ulonglong2 v = *(const ulonglong2*)(a.src[i] + ((size_t)p * a.stride[i] + t) * N + x);
+        const u64 k = a.k[i * LINCOMB_LIMBS + t];
+        acc.x = add_mod(acc.x, barrett_mul(v.x, k, m), m.q);
+        acc.y = add_mod(acc.y, barrett_mul(v.y, k, m), m.q);
+    }
+    if (has_c0 && p == 0) {
+        const u64 c = a.k[n * LINCOMB_LIMBS + t];
+        acc.x = add_mod(acc.x, c, m.q); acc.y = add_mod(acc.y, c, m.q);
+    }
+    *(ulonglong2*)(out + ((size_t)p * L + t) * N + x) = acc;
+}
+
 __global__ void __launch_bounds__(TPB)
 tensor_kernel(const u64* __restrict__ a, int a_stride, const u64* __restrict__ b, int b_stride,
               u64* __restrict__ out, int L, int N, const ModConst* __restrict__ mc) {
@@ -147,6 +178,19 @@ void ew_add_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_str
     ScalarTab tab; DevBuf buf; const ulonglong2* s = stage_scalars(c, limbs, L, scalars, tab, buf);
     dim3 grid(c.N / (2 * TPB), limbs, polys);
     OB_LAUNCH((ew_scalar_kernel<1>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), tab, s, only_poly);
+}
+
+void lin_comb(Context& c, int n, const u64* const* src, const int* stride, const std::vector<std::vector<u64>>& k,
+              const std::vector<u64>* c0, u64* out, int polys, int L) {
+    OB_CHECK(n >= 1 && n <= LINCOMB_MAX && L <= LINCOMB_LIMBS, "lin_comb: too many terms or limbs");
+    LinCombArgs a;
+    for (int i = 0; i < n; ++i) {
+        a.src[i] = src[i]; a.stride[i] = stride[i];
+        for (int t = 0; t < L; ++t) a.k[i * LINCOMB_LIMBS + t] = k[i][t];
+    }
+    if (c0) for (int t = 0; t < L; ++t) a.k[n * LINCOMB_LIMBS + t] = (*c0)[t];
+    dim3 grid(c.N / (2 * TPB), L, polys);
+    OB_LAUNCH(lincomb_kernel, grid, TPB, 0, stream(), a, n, c0 ? 1 : 0, out, L, c.N, c.dmc());
 }
 
 void tensor_product(Context& c, const u64* a, int a_stride, const u64* b, int b_stride, u64* out, int L) {

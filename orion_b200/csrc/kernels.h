@@ -18,6 +18,11 @@ void ew_add_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_str
                    const std::vector<u64>& scalars, int only_poly);
 // degree-2 tensor product: (d0,d1,d2) = (a0*b0, a0*b1 + a1*b0, a1*b1), L limbs each (chain index = limb)
 void tensor_product(Context& c, const u64* a, int a_stride, const u64* b, int b_stride, u64* out, int L);
+// out[p][t] = sum_{i<n} k[i][t] * src_i[p][t] (+ c0[t] on p = 0) over the first L limbs of the Q chain; src_i has `stride[i]`
+// limbs per polynomial (>= L), out has L.  One launch (kernels.cu lincomb_kernel).
+constexpr int LINCOMB_MAX = 16, LINCOMB_LIMBS = 96;
+void lin_comb(Context& c, int n, const u64* const* src, const int* stride, const std::vector<std::vector<u64>>& k,
+              const std::vector<u64>* c0, u64* out, int polys, int L);
 // NTT-domain automorphism: out[p][t][i] = in[p][t][idx[i]]
 void automorphism_ntt(Context& c, const u64* in, u64* out, int total_limbs, const uint32_t* idx);
 // to / from Montgomery form (x * 2^64 mod q), limbs laid out like ew_binary

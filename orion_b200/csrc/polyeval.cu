@@ -121,24 +121,20 @@ struct Evaluator {
         for (int i = 1; i <= deg; ++i)
             if (p[i] != 0.0 && !(in_basis(i) && pb.level_of(i, in_level) >= L)) direct = false;
         if (direct) {
-            std::unique_ptr<Ciphertext> acc;
-            for (int i = 1; i <= deg; ++i) {
-                if (p[i] == 0.0) continue;
-                const Ciphertext& Pi = pb.get(i);
-                std::unique_ptr<Ciphertext> src;
-                const Ciphertext* use = &Pi;
-                if (Pi.level > L) { src = s.clone(Pi); s.drop_level(*src, L); use = src.get(); }
-                auto term = std::make_unique<Ciphertext>();
-                s.mul_const_scaled(*use, p[i], S / use->scale, *term);
-                term->scale = S;
-                if (!acc) acc = std::move(term); else s.add_ct(*acc, *term, *acc, false);
+            // leaf: sum_i round(c_i * S/s_i) * P_i + round(c_0 * S) -- one fused launch (Scheme::lin_comb_scaled); powers that
+            // sit above level L are read in place with their own limb stride instead of being copied down
+            std::vector<const Ciphertext*> ops; std::vector<double> cs;
+            for (int i = 1; i <= deg; ++i)
+                if (p[i] != 0.0) { ops.push_back(&pb.get(i)); cs.push_back(p[i]); }
+            auto acc = std::make_unique<Ciphertext>();
+            if (!ops.empty()) {
+                s.lin_comb_scaled(ops, cs, p[0], L, S, *acc);
+                return acc;
             }
-            if (!acc) {                                            // constant polynomial: 0 * P_1 + c_0
-                auto c = s.clone(pb.get(1)); s.drop_level(*c, L);
-                acc = std::make_unique<Ciphertext>();
-                s.mul_int(*c, 0, *acc);
-                acc->scale = S;
-            }
+            // constant polynomial: 0 * P_1 + c_0
+            auto c = s.clone(pb.get(1)); s.drop_level(*c, L);
+            s.mul_int(*c, 0, *acc);
+            acc->scale = S;
             if (p[0] != 0.0) s.add_const(*acc, p[0], *acc);
             return acc;
         }

@@ -121,6 +121,10 @@ class Scheme {
     void mul_int(const Ciphertext& a, long long k, Ciphertext& out);
     void mul_float(const Ciphertext& a, double c, Ciphertext& out);         // * round(c*q_level), scale *= q_level
     void mul_const_scaled(const Ciphertext& a, double c, scale_t cscale, Ciphertext& out);  // * round(c*cscale)
+    // out = sum_i round(c_i * S / scale(a_i)) * a_i  (+ round(c0 * S)) at `level` (operands may sit higher), scale exactly S:
+    // the same residues as mul_const_scaled + add_ct + add_const term by term, in one launch per 16 terms
+    void lin_comb_scaled(const std::vector<const Ciphertext*>& a, const std::vector<double>& c, double c0, int level, scale_t S,
+                         Ciphertext& out);
     void mul_relin(const Ciphertext& a, const Ciphertext& b, Ciphertext& out, bool relin = true);
     void relinearize(Ciphertext& a);
     void rescale(const Ciphertext& a, Ciphertext& out);
