@@ -330,8 +330,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
         for (int k = 0; k < b.r; ++k) {
             Ciphertext sq;
             bs.mul_relin(*y, *y, sq);
-            bs.mul_int(sq, 2, sq);
-            bs.add_const(sq, -1.0, sq);
+            bs.lin_comb_int({&sq}, {2.0L}, -roundl(sq.scale), sq.level, sq.scale, sq);      // 2 c^2 - 1 in one launch
             bs.rescale(sq, *y);
         }
         return y;

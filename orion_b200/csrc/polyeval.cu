@@ -39,17 +39,16 @@ struct PowerBasis {
         auto prod = std::make_unique<Ciphertext>();
         s.mul_relin(A, Bc, *prod);
         if (cheb) {
-            s.mul_int(*prod, 2, *prod);
+            // T_{a+b} = 2 T_a T_b - T_{a-b}: the doubling and the subtraction in one fused launch.  T_{a-b} is multiplied by
+            // the integer k = round(scale(T_a T_b) / scale(T_{a-b})) so the scales match up to 1/k; T_0 = 1 is the constant
+            // round(scale).  Same residues as mul_int(2), mul_const(k) and a subtraction.
             const int c = a - b;
             if (c == 0) {
-                s.add_const(*prod, -1.0, *prod);
+                s.lin_comb_int({prod.get()}, {2.0L}, -roundl(prod->scale), prod->level, prod->scale, *prod);
             } else {
                 const Ciphertext& C = get(c);
-                Ciphertext tc;
                 const scale_t k = roundl(prod->scale / C.scale);
-                s.mul_const_scaled(C, 1.0, k, tc);
-                tc.scale = prod->scale;                             // matched up to 1/k
-                s.add_ct(*prod, tc, *prod, true);
+                s.lin_comb_int({prod.get(), &C}, {2.0L, -k}, 0.0L, prod->level, prod->scale, *prod);
             }
         }
         s.rescale(*prod, *prod);

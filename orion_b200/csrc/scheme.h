@@ -123,6 +123,9 @@ class Scheme {
     void mul_const_scaled(const Ciphertext& a, double c, scale_t cscale, Ciphertext& out);  // * round(c*cscale)
     // out = sum_i round(c_i * S / scale(a_i)) * a_i  (+ round(c0 * S)) at `level` (operands may sit higher), scale exactly S:
     // the same residues as mul_const_scaled + add_ct + add_const term by term, in one launch per 16 terms
+    // out = sum_i k_i * a_i (+ c0) with explicit signed integer multipliers (integer-valued long doubles), scale `S` as given
+    void lin_comb_int(const std::vector<const Ciphertext*>& a, const std::vector<long double>& k, long double c0, int level,
+                      scale_t S, Ciphertext& out);
     void lin_comb_scaled(const std::vector<const Ciphertext*>& a, const std::vector<double>& c, double c0, int level, scale_t S,
                          Ciphertext& out);
     void mul_relin(const Ciphertext& a, const Ciphertext& b, Ciphertext& out, bool relin = true);

@@ -106,24 +106,34 @@ void Scheme::mul_const_scaled(const Ciphertext& a, double c, scale_t cscale, Cip
 void Scheme::lin_comb_scaled(const std::vector<const Ciphertext*>& a, const std::vector<double>& c, double c0, int level,
                              scale_t S, Ciphertext& out) {
     OB_CHECK(!a.empty() && a.size() == c.size(), "lin_comb_scaled: bad operand list");
+    std::vector<long double> k(a.size());
+    for (size_t i = 0; i < a.size(); ++i) {
+        const long double v = roundl(fabsl((long double)c[i] * (S / a[i]->scale)));       // as mul_const_scaled(a_i, c_i, S/s_i)
+        k[i] = c[i] < 0 ? -v : v;
+    }
+    const long double v0 = roundl(fabsl((long double)c0 * S));                            // as add_const at scale S
+    lin_comb_int(a, k, c0 < 0 ? -v0 : v0, level, S, out);
+}
+void Scheme::lin_comb_int(const std::vector<const Ciphertext*>& a, const std::vector<long double>& kk, long double c0, int level,
+                          scale_t S, Ciphertext& out) {
+    OB_CHECK(!a.empty() && a.size() == kk.size(), "lin_comb_int: bad operand list");
     const int L = level + 1, polys = a[0]->degree + 1;
     auto tmp = new_ct(level, a[0]->degree, S, a[0]->log_slots);
-    std::unique_ptr<Ciphertext> part;                                    // running sum when there are more than 16 terms
+    std::unique_ptr<Ciphertext> part;                                    // running sum when there are more than 15 terms
     for (size_t i0 = 0; i0 < a.size(); i0 += LINCOMB_MAX - 1) {
         const size_t m = std::min<size_t>(LINCOMB_MAX - 1, a.size() - i0);
         std::vector<const u64*> src; std::vector<int> stride; std::vector<std::vector<u64>> k;
         if (part) { src.push_back(part->data.u()); stride.push_back(L); k.push_back(const_to_rns(*ctx, 1.0L, false, L, L)); }
         for (size_t i = i0; i < i0 + m; ++i) {
-            OB_CHECK(a[i]->level >= level && a[i]->degree + 1 == polys, "lin_comb_scaled: operand below the target level");
-            const long double v = roundl(fabsl((long double)c[i] * (S / a[i]->scale)));
+            OB_CHECK(a[i]->level >= level && a[i]->degree + 1 == polys, "lin_comb: operand below the target level");
             src.push_back(a[i]->data.u()); stride.push_back(a[i]->level + 1);
-            k.push_back(const_to_rns(*ctx, v, c[i] < 0, L, L));
+            k.push_back(const_to_rns(*ctx, fabsl(kk[i]), kk[i] < 0, L, L));
         }
         const bool last = i0 + m >= a.size();
         std::vector<u64> k0;
-        if (last && c0 != 0.0) k0 = const_to_rns(*ctx, roundl(fabsl((long double)c0 * S)), c0 < 0, L, L);
+        if (last && c0 != 0.0L) k0 = const_to_rns(*ctx, fabsl(c0), c0 < 0, L, L);
         auto dst = last ? nullptr : new_ct(level, a[0]->degree, S, a[0]->log_slots);
-        lin_comb(*ctx, (int)src.size(), src.data(), stride.data(), k, (last && c0 != 0.0) ? &k0 : nullptr,
+        lin_comb(*ctx, (int)src.size(), src.data(), stride.data(), k, (last && c0 != 0.0L) ? &k0 : nullptr,
                  last ? tmp->data.u() : dst->data.u(), polys, L);
         if (!last) part = std::move(dst);
     }
