@@ -34,6 +34,8 @@ def build(force=False):
         subprocess.check_call(["make", "-C", _HERE, "libckks_oracle.so"], stdout=subprocess.DEVNULL)
     if os.path.isdir("/root/reference") and (force or not os.path.exists(os.path.join(_HERE, "_ref", "libgpuntt_ref.so"))):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference") and (force or not os.path.exists(os.path.join(_HERE, "_ref", "libgpuntt_refgpu.so"))):
+        subprocess.check_call(["make", "-C", _HERE, "refgpu"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     return so
 
 
@@ -134,6 +136,34 @@ def ref():
     for f in (R.ref_ntt_pool, R.ref_ntt_forward, R.ref_ntt_inverse, R.ref_schoolbook):
         f.restype = None
     _ref = R
+    return R
+
+
+_refgpu = None
+
+
+def ref_gpu():
+    """The reference's own GPU merge NTT (GPU-NTT ntt.cu, gpuntt::GPU_NTT_Inplace) compiled in place for sm_100a, or
+    None.  Needs a CUDA device to be called; loading does not."""
+    global _refgpu
+    if _refgpu is not None:
+        return _refgpu
+    so = os.path.join(_HERE, "_ref", "libgpuntt_refgpu.so")
+    if not os.path.exists(so):
+        return None
+    try:
+        R = ctypes.CDLL(so)
+    except OSError:
+        return None
+    R.refgpu_create.argtypes = [c_int, c_int, u64p, u64p]
+    R.refgpu_create.restype = c_vp
+    R.refgpu_destroy.argtypes = [c_vp]
+    R.refgpu_destroy.restype = None
+    R.refgpu_ntt_host.argtypes = [c_vp, u64p, u64p, c_int, c_int]
+    R.refgpu_ntt_host.restype = None
+    R.refgpu_time_ms.argtypes = [c_vp, c_int, c_int, c_int, c_int]
+    R.refgpu_time_ms.restype = ctypes.c_float
+    _refgpu = R
     return R
 
 

@@ -42,10 +42,10 @@ if "--host-time" in sys.argv:
     # host-side enqueue time per op type (no synchronisation added): how far the launch rate is from the GPU time
     import collections
     tsum, cnt = collections.Counter(), collections.Counter()
-    orig = r._run
+    base_run = r._run if "--by-op" not in sys.argv else orig
     def timed(i, op):
         t0 = time.perf_counter()
-        orig(i, op)
+        base_run(i, op)
         tsum[op[0]] += time.perf_counter() - t0; cnt[op[0]] += 1
     r._run = timed
     lib.B200_Sync(); t0 = time.perf_counter()
