@@ -46,16 +46,31 @@ bool hostprof_on();
 void hostprof_dump();
 #define OB_HP(name) static const int hp_slot__ = ::ob::hostprof_slot(name); ::ob::HostProf hp__(hp_slot__)
 bool dry_run();        // ORION_B200_DRYRUN=1: skip the launches (host-side enqueue cost measurement only; results are garbage)
+// Driver-API launch path (ORION_B200_DRIVER_LAUNCH=1; default off): the CUfunction of every kernel is resolved once
+// (cudaGetFuncBySymbol) and launched with cuLaunchKernelEx obtained through cudaGetDriverEntryPoint -- no libcuda link
+// dependency, no per-launch symbol lookup inside the runtime.  Measured on the ResNet-20 replay (58 k launches per image):
+// 3.4 -> 2.7 us of host time per launch, and no change of the 0.331 s/image -- with the dataflow lanes the replay is bounded
+// by the GPU-side dependency chains, not by the enqueue rate -- so the runtime path stays the default.
+bool driver_launch_enabled();
+void driver_launch(const void* kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, void** params);
 template <class... KArgs, class... Args>
 inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
     if (dry_run()) return;
+    OB_HP("cudaLaunchKernelEx");
+    if (driver_launch_enabled()) {
+        auto go = [&](KArgs... k) {
+            void* params[] = {(void*)&k...};
+            driver_launch((const void*)kernel, grid, block, smem, st, params);
+        };
+        go(KArgs(args)...);
+        return;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
-    OB_HP("cudaLaunchKernelEx");
     OB_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
 }
 #define OB_LAUNCH(kernel, grid, block, smem, stream, ...) do { \

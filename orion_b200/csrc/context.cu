@@ -2,6 +2,7 @@
 #include "context.h"
 #include <algorithm>
 #include <unordered_map>
+#include <cuda.h>
 
 namespace ob {
 
@@ -53,10 +54,11 @@ EvRef record_event(cudaStream_t s) {
     OB_CUDA(cudaEventRecord(r->e, s));
     return r;
 }
-// PDL policy: measured +3 % on the logN=16 key switch (tail of one kernel overlaps the head of the next) and -30 % on a
-// bare rescale chain, but -9 % on the ResNet-20 replay at logN=13, where early-resident dependents take SM slots from
-// the side streams' kernels.  Default: on for rings of degree >= 2^15, off below; ORION_B200_PDL=0/1 overrides.
-static bool g_pdl_auto = false;
+// PDL policy: measured +3 % on the logN=16 key switch (tail of one kernel overlaps the head of the next), -30 % on a
+// bare rescale chain, and on the ResNet-20 replay at logN=13: 0.373 -> 0.339 s/image with the dataflow lanes (before the
+// lanes it cost 9 % there: early-resident dependents took SM slots from the side streams' kernels; with eight lanes the
+// shorter kernel-to-kernel gap of every chain wins).  Default: on for every ring; ORION_B200_PDL=0/1 overrides.
+static bool g_pdl_auto = true;
 bool pdl_enabled() {
     static int forced = -2;
     if (forced == -2) { const char* s = std::getenv("ORION_B200_PDL"); forced = s ? (std::atoi(s) != 0) : -1; }
@@ -107,6 +109,48 @@ void hostprof_dump() {
         if (kv.second.second)
             std::fprintf(stderr, "hostprof %-28s n=%8llu  %9.2f ms  %7.2f us/call\n", kv.first.c_str(), kv.second.second,
                          kv.second.first / 1e6, kv.second.first / 1e3 / kv.second.second);
+}
+// ---- driver-API launch path (common.h) ----
+namespace {
+typedef CUresult (*CuLaunchKernelExFn)(const CUlaunchConfig*, CUfunction, void**, void**);
+CuLaunchKernelExFn g_cu_launch = nullptr;
+std::unordered_map<const void*, CUfunction>& fn_cache() { static auto* m = new std::unordered_map<const void*, CUfunction>(); return *m; }
+}
+bool driver_launch_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char* s = std::getenv("ORION_B200_DRIVER_LAUNCH");
+        on = (s && std::atoi(s) != 0) ? 1 : 0;
+        if (on) {
+            void* fp = nullptr;
+            cudaDriverEntryPointQueryResult qr;
+            if (cudaGetDriverEntryPoint("cuLaunchKernelEx", &fp, cudaEnableDefault, &qr) != cudaSuccess || !fp ||
+                qr != cudaDriverEntryPointSuccess) { cudaGetLastError(); on = 0; }
+            else g_cu_launch = (CuLaunchKernelExFn)fp;
+        }
+    }
+    return on == 1;
+}
+void driver_launch(const void* kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t st, void** params) {
+    auto& cache = fn_cache();
+    auto it = cache.find(kernel);
+    if (it == cache.end()) {
+        cudaFunction_t f = nullptr;
+        OB_CUDA(cudaGetFuncBySymbol(&f, kernel));
+        it = cache.emplace(kernel, (CUfunction)f).first;
+    }
+    CUlaunchConfig cfg;
+    std::memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDimX = grid.x; cfg.gridDimY = grid.y; cfg.gridDimZ = grid.z;
+    cfg.blockDimX = block.x; cfg.blockDimY = block.y; cfg.blockDimZ = block.z;
+    cfg.sharedMemBytes = (unsigned)smem; cfg.hStream = (CUstream)st;
+    CUlaunchAttribute attr;
+    std::memset(&attr, 0, sizeof(attr));
+    attr.id = CU_LAUNCH_ATTRIBUTE_PROGRAMMATIC_STREAM_SERIALIZATION;
+    attr.value.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    const CUresult r = g_cu_launch(&cfg, it->second, params, nullptr);
+    if (r != CUDA_SUCCESS) OB_FATAL("cuLaunchKernelEx failed with CUresult " + std::to_string((int)r));
 }
 bool dry_run() {
     static int on = -1;
@@ -309,7 +353,7 @@ static void upload(DevBuf& d, const std::vector<T>& h) {
 Context::Context(int logN_, const std::vector<u64>& Q, const std::vector<u64>& P) {
     ensure_device();
     logN = logN_; N = 1 << logN; nQ = (int)Q.size(); nP = (int)P.size(); nmod = nQ + nP;
-    g_pdl_auto = logN >= 15;
+    g_pdl_auto = true;
     OB_CHECK(logN >= 10 && logN <= 17, "logN must be within 10..17");
     OB_CHECK(nmod <= 64, "at most 64 moduli");
     mod = Q; mod.insert(mod.end(), P.begin(), P.end());

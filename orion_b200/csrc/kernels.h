@@ -46,8 +46,9 @@ struct BcDev {
     const int* src_mod; const int* dst_mod; const LimbDesc* out_off;
     const ulonglong2* inv; const u64* mat; const u64* negvq; const u64* half_src; const u64* half_dst;
     const double* mat_d; const double* negvq_d; int f64_src;
+    int mm;                       // integer-path accumulation mode of this conversion (ks_kernels.cu: 0 / 1 raw / 2 96-bit)
 };
-struct BaseConvBatch { const BcDev* dev = nullptr; int n = 0; size_t smem = 0; int max_ns = 0; int min_nd = 1 << 30; };
+struct BaseConvBatch { const BcDev* dev = nullptr; int n = 0; size_t smem = 0; int max_ns = 0; int min_nd = 1 << 30; int mac_mode = 0; };
 BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& plans, const std::vector<int>& in_off,
                                   const std::vector<int>& out_base);
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered);

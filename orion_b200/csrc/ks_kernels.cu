@@ -72,11 +72,24 @@ __device__ __forceinline__ void mac128_raw(u64& hi, u64& lo, u64 a, u64 b) {
     lo += pl;
     hi += ph + (lo < pl);
 }
+// 96-bit multiply-accumulate for a 32-bit residue (every source prime below 2^32, e.g. the 30-bit primes of the shipped
+// ResNet-20 chain): two IMAD.WIDE instead of four, no high-word reduction
+__device__ __forceinline__ void mac96_raw(u64& hi, u64& lo, uint32_t a, u64 b) {
+    const u64 p0 = (u64)a * (uint32_t)b, p1 = (u64)a * (uint32_t)(b >> 32);
+    const u64 l = p0 + (p1 << 32);
+    lo += l;
+    hi += (p1 >> 32) + (l < p0) + (lo < l);
+}
+// MM = highest accumulation mode of the integer path over the conversions of the batch (BcDev::mm is per conversion),
+// chosen on the host from the source primes:
+//   0: mac128 (conditional high-word reduction after every term)
+//   1: mac128_raw -- valid when sum_i q_src_i <= 2^64: sum_i y_i*w_i < q_t * 2^64, which is all REDC needs
+//   2: mac96_raw  -- additionally every source prime is below 2^32
 // NS = compile-time bound on the source-limb count of every conversion in the batch.  VEC = adjacent coefficients per
 // thread (2: 128-bit loads/stores and every per-destination constant fetched once for both -- large rings; 1: twice
 // the threads -- small rings).  gridDim.z splits the destination limbs into chunks so that a conversion of a small
 // ring (logN = 13, 8 x 61-bit special primes in the bootstrapping chain) still fills the 148 SMs.
-template <bool CENTERED, int NS, int VEC>
+template <bool CENTERED, int NS, int VEC, int MM>
 __global__ void __launch_bounds__(BC_TPB)
 baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                       const ModConst* __restrict__ mc) {
@@ -101,6 +114,7 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     ulonglong2* s_inv = (ulonglong2*)(s_sqd + ns + (ns & 1));   // [ns], 16-byte aligned
     int* s_off = (int*)(s_inv + ns);                   // [chunk]
     const bool f64 = !CENTERED && d.f64_src;
+    const int mm = d.mm;                               // this conversion's accumulation mode (CTA-uniform), at most MM
     for (int i = threadIdx.x; i < ns * ndc; i += BC_TPB) {
         const int r = i / ndc, t = i - r * ndc;
         s_mat[r * chunk + t] = d.mat[r * nd + t0 + t]; s_matd[r * chunk + t] = d.mat_d[r * nd + t0 + t];
@@ -194,7 +208,9 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
                     const u64 w = s_mat[i * chunk + t];
 #pragma unroll
                     for (int c = 0; c < VEC; ++c) {
-                        if (NS <= 3) mac128_raw(hi[c], lo[c], y[c][i], w); else mac128(hi[c], lo[c], y[c][i], w, q);
+                        if (MM == 2 && mm == 2) mac96_raw(hi[c], lo[c], (uint32_t)y[c][i], w);
+                        else if ((MM >= 1 && mm >= 1) || NS <= 3) mac128_raw(hi[c], lo[c], y[c][i], w);
+                        else mac128(hi[c], lo[c], y[c][i], w, q);
                     }
                 }
             const u64 qi = s_dqi[t];
@@ -354,12 +370,17 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
         const BaseConv& bc = *plans[z].bc;
         h[z] = BcDev{bc.ns, bc.nd, in_off[z], out_base[z], bc.src_mod.as<int>(), bc.dst_mod.as<int>(), plans[z].out_off,
                      bc.inv.as<ulonglong2>(), bc.mat.u(), bc.negvq.u(), bc.half_src.u(), bc.half_dst.u(),
-                     bc.mat_d.as<double>(), bc.negvq_d.as<double>(), bc.f64_src ? 1 : 0};
+                     bc.mat_d.as<double>(), bc.negvq_d.as<double>(), bc.f64_src ? 1 : 0, 0};
         const size_t ns = bc.ns, nd = bc.nd;
         const size_t sm = 8 * (2 * (ns * nd + nd * (ns + 1)) + 4 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 8 * nd + 16;
         b.smem = std::max(b.smem, sm);
         b.max_ns = std::max(b.max_ns, bc.ns);
         b.min_nd = std::min(b.min_nd, bc.nd);
+        unsigned __int128 qsum = 0;
+        bool small = true;
+        for (int i : bc.h_src) { qsum += c.mod[i]; small = small && c.mod[i] < (1ull << 32); }
+        h[z].mm = qsum <= ((unsigned __int128)1 << 64) ? (small ? 2 : 1) : 0;
+        b.mac_mode = std::max(b.mac_mode, h[z].mm);
     }
     auto buf = std::make_unique<DevBuf>(h.size() * sizeof(BcDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, h.data(), h.size() * sizeof(BcDev), cudaMemcpyHostToDevice, stream()));
@@ -379,11 +400,13 @@ void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* 
     const long thr = ((long)c.N / vec) * b.n;
     int nsplit = (int)std::min<long>(std::max<long>(1, (want + thr - 1) / thr), std::max(1, b.min_nd / 4));
     dim3 grid(c.N / (vec * BC_TPB), b.n, nsplit);
-#define OB_BC2(C, NSV) do { if (vec == 2) OB_LAUNCH((baseconv_batch_kernel<C, NSV, 2>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); \
-                            else OB_LAUNCH((baseconv_batch_kernel<C, NSV, 1>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+#define OB_BC3(C, NSV, MMV) do { if (vec == 2) OB_LAUNCH((baseconv_batch_kernel<C, NSV, 2, MMV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); \
+                            else OB_LAUNCH((baseconv_batch_kernel<C, NSV, 1, MMV>), grid, BC_TPB, b.smem, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+#define OB_BC2(C, NSV) do { if (b.mac_mode == 2) OB_BC3(C, NSV, 2); else if (b.mac_mode == 1 && NSV > 3) OB_BC3(C, NSV, 1); else OB_BC3(C, NSV, 0); } while (0)
 #define OB_BC(NSV) do { if (centered) OB_BC2(true, NSV); else OB_BC2(false, NSV); } while (0)
     if (b.max_ns <= 1) OB_BC(1); else if (b.max_ns <= 2) OB_BC(2); else if (b.max_ns <= 3) OB_BC(3); else if (b.max_ns <= 4) OB_BC(4);
     else if (b.max_ns <= 6) OB_BC(6); else if (b.max_ns <= 8) OB_BC(8); else OB_BC(MAX_NS);
+#undef OB_BC3
 #undef OB_BC2
 #undef OB_BC
 }

@@ -12,6 +12,8 @@ CASES = [  # (logN, LogQ, LogP)
     (16, [60, 46, 45, 47, 46], [61, 46]),              # both sides of the FP64 / integer butterfly split (46 bits)
     (15, [46, 46, 46, 46], [46, 46]),                  # FP64 butterflies only, largest admissible primes
     (17, [45, 45], [45]),                              # deepest transform (17 stages) on the FP64 path
+    (13, [60] + [30] * 16, [61] * 8),                  # bootstrapping-style chain: 8 special primes, 30-bit digits (raw / 96-bit MAC modes)
+    (13, [30] * 9, [61] * 8),                          # every ModUp source below 2^32 (96-bit MAC mode for the whole batch)
 ]
 
 
