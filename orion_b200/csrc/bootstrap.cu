@@ -30,7 +30,10 @@ typedef std::complex<double> cd;
 typedef std::map<int, std::vector<cd>> DiagMat;       // rotation -> diagonal (length n)
 
 constexpr int TPB = 256;
-constexpr int CTS_DEPTH = 4, STC_DEPTH = 3, CHEB_DEPTH = 6, LOG_MSG_RATIO = 10;
+constexpr int CHEB_DEPTH = 6, LOG_MSG_RATIO = 10;
+// levels (= merged DFT factor matrices) spent on CoeffsToSlots / SlotsToCoeffs; ORION_B200_CTS_DEPTH / _STC_DEPTH override
+static int env_depth(const char* name, int dflt) { const char* s = std::getenv(name); const int v = s ? std::atoi(s) : dflt; return v >= 1 && v <= 8 ? v : dflt; }
+static const int CTS_DEPTH = env_depth("ORION_B200_CTS_DEPTH", 4), STC_DEPTH = env_depth("ORION_B200_STC_DEPTH", 3);
 
 // out[p][i][x] = centred(in[p][x] mod q0) mod q_i      (coefficient domain)
 __global__ void __launch_bounds__(TPB)

@@ -17,6 +17,7 @@
 // __syncthreads with Barrett multiplication; this is a different design, not a port.
 #include "context.h"
 #include "kernels.h"
+#include <cooperative_groups.h>
 
 namespace ob {
 
@@ -234,21 +235,36 @@ __device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], 
 // scales by N^-1 for INV).
 // KEEP (contiguous forward final pass only): the results stay in registers -- thread tid returns words [8 tid, 8 tid + 8)
 // of the tile as policy values (A::keep) instead of storing them.
-template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL, bool KEEP = false>
+// IO (cluster kernel, ntt_cluster below): 0 = global memory at both ends; 1 = the pass's output goes to the cluster's
+// distributed shared-memory staging buffer (`stage` = this CTA's 2048-word slice; word g of the limb lives in the slice of
+// the CTA that transforms it next); 2 = the pass's input comes from this CTA's slice.  tile_ / tid_ replace blockIdx.x /
+// threadIdx.x when a CTA walks several tiles or runs two tiles side by side.
+template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL, bool KEEP = false, int IO = 0>
 __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restrict__ src, u64* __restrict__ dst,
                                          const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN,
-                                         typename A::T* kept = nullptr, const bool raw_in = false) {
+                                         typename A::T* kept = nullptr, const bool raw_in = false,
+                                         u64* stage = nullptr, const int tile_ = -1, const int tid_ = -1) {
     typedef typename A::T T;
     constexpr int LOG_EPT = log_ept(STRIDED, FWD), EPT = 1 << LOG_EPT;
     constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
-    const int tid = threadIdx.x;
+    const int tid = tid_ < 0 ? (int)threadIdx.x : tid_;
+    const int tile = tile_ < 0 ? (int)blockIdx.x : tile_;
     constexpr int logC = STRIDED ? LOG_E - nbits : 0;
     constexpr int lo_bit = STRIDED ? logC : 0;           // lowest transformed local bit
     const int TOP = STRIDED ? LOG_E - 1 : logN - 1;      // stage = TOP - local bit
-    const int tile_base = STRIDED ? 0 : blockIdx.x << LOG_E;
+    const int tile_base = STRIDED ? 0 : tile << LOG_E;
     auto gidx = [&](int li) -> int {
-        if (STRIDED) return ((li >> logC) << (logN - nbits)) + (blockIdx.x << logC) + (li & ((1 << logC) - 1));
+        if (STRIDED) return ((li >> logC) << (logN - nbits)) + (tile << logC) + (li & ((1 << logC) - 1));
         return tile_base + li;
+    };
+    // cluster staging (IO != 0): the strided tiles are 2048 words with 2^(19 - logN) columns; word g of the limb is staged
+    // for the contiguous pass in slice g >> 11 at g & 2047, for the strided pass in slice (g & 255) >> logCs at
+    // ((g >> 8) << logCs) | (g & (Cs - 1))
+    auto stage_ptr = [&](int g) -> u64* {
+        const int logCs = 19 - logN;
+        const int rank = FWD ? (g >> 11) : ((g & 255) >> logCs);
+        const int loc = FWD ? (g & 2047) : (((g >> 8) << logCs) | (g & ((1 << logCs) - 1)));
+        return cooperative_groups::this_cluster().map_shared_rank(stage, rank) + loc;
     };
 
     constexpr int NR = (NBITS + LOG_EPT - 1) / LOG_EPT, RBASE = NBITS / NR, REXTRA = NBITS % NR;
@@ -265,13 +281,14 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
         const int pair_step = pos == 0 ? 1 : (G >= 2 ? (1 << nb) : 0);
         // per group g: local index with the round's k bits zero, its shared-memory slot and its word index in the limb;
         // element (g, k) adds compile-time offsets to both
-        T v[EPT]; int sbase[EPT], gbase[EPT], twb[EPT];
+        T v[EPT]; int sbase[EPT], gbase[EPT], twb[EPT], lbase[EPT];
 #pragma unroll
         for (int g = 0; g < EPT; ++g) {
             if (g < G) {
                 const int base = insert_bits(tid * G + g, pos, nb, 0);
                 sbase[g] = pad<LOG_EPT>(base);
                 gbase[g] = gidx(base);
+                lbase[g] = base + (STRIDED ? 0 : ((tile & 1) << LOG_E));      // IO == 2: word index in this CTA's slice
             }
             twb[g] = (1 << (TOP - ptop)) + ((tid * G + g) >> pos) + (tile_base >> (ptop + 1));
         }
@@ -283,7 +300,10 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
         const bool quad = pos == 0 && nb >= 2;            // a thread owns runs of >= 4 adjacent words: 256-bit accesses
         if (r == 0) {
             u64 w[EPT];
-            if (quad) {
+            if (IO == 2) {
+#pragma unroll
+                for (int e = 0; e < EPT; ++e) w[e] = stage[lbase[e >> nb] + ((e & ((1 << nb) - 1)) << pos)];
+            } else if (quad) {
 #pragma unroll
                 for (int e = 0; e < EPT; e += 4) ld_global_256(src + goff(e), w[e], w[e + 1], w[e + 2], w[e + 3]);
             } else if (pair_step) {
@@ -323,7 +343,16 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
             u64 w[EPT];
 #pragma unroll
             for (int e = 0; e < EPT; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
-            if (quad) {
+            if (IO == 1) {
+                if (pair_step) {
+#pragma unroll
+                    for (int e = 0; e < EPT; ++e)
+                        if (!(e & pair_step)) *(ulonglong2*)stage_ptr(goff(e)) = make_ulonglong2(w[e], w[e + pair_step]);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < EPT; ++e) *stage_ptr(goff(e)) = w[e];
+                }
+            } else if (quad) {
 #pragma unroll
                 for (int e = 0; e < EPT; e += 4) st_global_256(dst + goff(e), w[e], w[e + 1], w[e + 2], w[e + 3]);
             } else if (pair_step) {
@@ -484,7 +513,90 @@ ntt2_submul_kernel(const u64* __restrict__ a, int a_stride, const u64* __restric
         ntt2_submul_body<ArithInt>(ArithInt(m), sm, ap, bp, ad, op, tw_all + (size_t)i * N, mulc[i], m.q, logN);
 }
 
+// Whole-limb NTT / INTT in ONE launch for small rings (2^12 <= N <= 2^14): a thread-block cluster of N/2048 CTAs owns one
+// limb.  Forward: every CTA runs the strided pass on its 2048-word tile and scatters the lazy results through distributed
+// shared memory into the slice of the CTA that owns the destination words; after one cluster barrier every CTA runs the
+// contiguous pass on the two 1024-word tiles of its slice.  Inverse: the mirror image (two contiguous tiles side by side
+// on 256 threads, then the strided final pass).  Same ntt_body, same words as the two-launch path -- the inter-pass limb
+// never touches global memory and a transform is one link of a launch-latency-bound chain instead of two.
+// MEASURED, NOT ADOPTED (ORION_B200_CLUSTER_NTT=1 enables it for transforms of at most ORION_B200_CLUSTER_NTT_MAX = 48
+// limbs): bit-identical words, ResNet-20 at logN=13 57.7 k -> 48.5 k launches per image, but 0.3365 vs 0.3359 s/image and
+// LoLA2 at logN=14 2.43 vs 2.31 ms/image -- the two cluster barriers and the scatter through distributed shared memory
+// cost what the saved launch gains, and above ~100 limbs the two-launch path is faster (864 limbs: 54 vs 58 us).
+template <int NBITS, bool FWD>
+__global__ void __launch_bounds__(FWD ? 128 : 256)
+ntt_cluster(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
+            const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all,
+            const ulonglong2* __restrict__ ninv_all, int logN, int raw_flag) {
+    OB_PDL_SYNC();
+    namespace cg = cooperative_groups;
+    __shared__ __align__(16) u64 stage[1 << LOG_E_STRIDED];
+    __shared__ __align__(16) u64 sm[(1 << LOG_E_STRIDED) + (1 << (LOG_E_STRIDED - 3))];
+    cg::cluster_group cl = cg::this_cluster();
+    const int rank = (int)cl.block_rank();
+    const LimbDesc ld = limbs[blockIdx.y];
+    const size_t N = (size_t)1 << logN;
+    const ModConst& m = mc[ld.mod];
+    const u64* src = in + (size_t)ld.in_off * N;
+    u64* dst = out + (size_t)ld.out_off * N;
+    const ulonglong2 ni = ninv_all[ld.mod];
+    const bool f64 = m.bits <= F64_MAX_BITS;
+    const int tid = threadIdx.x;
+    constexpr int SM_C = (1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3));
+    cl.sync();                                   // every CTA of the cluster is resident before its slice is written
+    if (FWD) {
+        const bool raw_in = raw_flag && (ld.aux & 1);
+        if (f64) ntt_body<ArithF64, LOG_E_STRIDED, NBITS, true, true, false, false, 1>(ArithF64(m), sm, src, nullptr, twd_all + (size_t)ld.mod * N, ni, logN, nullptr, raw_in, stage, rank, tid);
+        else     ntt_body<ArithInt, LOG_E_STRIDED, NBITS, true, true, false, false, 1>(ArithInt(m), sm, src, nullptr, tw_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, rank, tid);
+        cl.sync();
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
+            if (f64) ntt_body<ArithF64, LOG_E_CONTIG, K2_BITS, false, true, true, false, 2>(ArithF64(m), sm, nullptr, dst, twd_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, 2 * rank + h, tid);
+            else     ntt_body<ArithInt, LOG_E_CONTIG, K2_BITS, false, true, true, false, 2>(ArithInt(m), sm, nullptr, dst, tw_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, 2 * rank + h, tid);
+            __syncthreads();
+        }
+    } else {
+        const int h = tid >> 7, t7 = tid & 127;
+        if (f64) ntt_body<ArithF64, LOG_E_CONTIG, K2_BITS, false, false, false, false, 1>(ArithF64(m), sm + h * SM_C, src, nullptr, twd_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, 2 * rank + h, t7);
+        else     ntt_body<ArithInt, LOG_E_CONTIG, K2_BITS, false, false, false, false, 1>(ArithInt(m), sm + h * SM_C, src, nullptr, tw_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, 2 * rank + h, t7);
+        cl.sync();
+        if (f64) ntt_body<ArithF64, LOG_E_STRIDED, NBITS, true, false, true, false, 2>(ArithF64(m), sm, nullptr, dst, twd_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, rank, tid);
+        else     ntt_body<ArithInt, LOG_E_STRIDED, NBITS, true, false, true, false, 2>(ArithInt(m), sm, nullptr, dst, tw_all + (size_t)ld.mod * N, ni, logN, nullptr, false, stage, rank, tid);
+    }
+}
+
 }  // namespace
+
+// cluster launch: grid (N/2048, limbs), cluster (N/2048, 1, 1)
+bool cluster_ntt_enabled(const Context& c, int limbs) {
+    static int on = -1, max_limbs = 0;
+    if (on < 0) {
+        const char* s = std::getenv("ORION_B200_CLUSTER_NTT"); on = (s && std::atoi(s) != 0) ? 1 : 0;
+        const char* m = std::getenv("ORION_B200_CLUSTER_NTT_MAX"); max_limbs = m ? std::atoi(m) : 48;
+    }
+    return on == 1 && c.logN >= 12 && c.logN <= 14 && limbs <= max_limbs;
+}
+template <class... KArgs, class... Args>
+static void launch_cluster(void (*kernel)(KArgs...), dim3 grid, int threads, int cluster_x, Args... args) {
+    g_launches++;
+    if (dry_run()) return;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = 0; cfg.stream = stream();
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cluster_x; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    OB_HP("cudaLaunchKernelEx");
+    OB_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+}
+#define OB_NTT_CLUSTER(FWD, ...) \
+    switch (c.logN - K2_BITS) { \
+        case 4: launch_cluster(ntt_cluster<4, FWD>, dim3(c.N >> LOG_E_STRIDED, p.n), FWD ? 128 : 256, c.N >> LOG_E_STRIDED, __VA_ARGS__); break; \
+        case 5: launch_cluster(ntt_cluster<5, FWD>, dim3(c.N >> LOG_E_STRIDED, p.n), FWD ? 128 : 256, c.N >> LOG_E_STRIDED, __VA_ARGS__); break; \
+        case 6: launch_cluster(ntt_cluster<6, FWD>, dim3(c.N >> LOG_E_STRIDED, p.n), FWD ? 128 : 256, c.N >> LOG_E_STRIDED, __VA_ARGS__); break; \
+        default: OB_FATAL("cluster NTT: unsupported logN"); }
 
 NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
     OB_HP("make_ntt_plan");
@@ -512,6 +624,10 @@ NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs) {
 // Batched forward NTT: limb i is read at in + in_off*N and written at out + out_off*N.
 void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
+    if (cluster_ntt_enabled(c, p.n)) {
+        OB_NTT_CLUSTER(true, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN, 1)
+        return;
+    }
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
     OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
@@ -563,6 +679,10 @@ void ntt2_submul(Context& c, int nl, int polys, const u64* a, int a_stride, cons
 
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
+    if (cluster_ntt_enabled(c, p.n)) {
+        OB_NTT_CLUSTER(false, in, out, p.first, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN, 0)
+        return;
+    }
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n), g2(c.N >> LOG_E_CONTIG, p.n);
     OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, false, false>), g2, 1 << (LOG_E_CONTIG - log_ept(false, true)), 0, stream(),

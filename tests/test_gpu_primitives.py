@@ -126,3 +126,15 @@ def test_keyswitch_stages_and_full(orc, b200lib, case):
     for ct, o in zip(cts, outs):
         assert np.array_equal(o, gc.keyswitch(level, ct[1], evk_dev))
     gc.lib.B200_DevFree(evk_dev)
+
+
+def test_cluster_ntt_switch_gives_the_same_words():
+    """ORION_B200_CLUSTER_NTT=1: whole-limb NTT in one thread-block-cluster launch (distributed shared memory between the
+    strided and the contiguous pass, csrc/ntt.cu ntt_cluster) for 2^12 <= N <= 2^14.  The switch is read once per process,
+    so the NTT parity cases (oracle and reference GPU kernel) are re-run in a child process with it on."""
+    import os, subprocess, sys
+    env = dict(os.environ, ORION_B200_CLUSTER_NTT="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_primitives.py", "tests/test_gpu_refgpu.py",
+                        "-k", "ntt_roundtrip or ntt_words or rescale or keyswitch_stages"], cwd=root, env=env, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
