@@ -122,7 +122,39 @@ def run_reference(args, rank, world):
                          "sample": "%d whole key switches at logN=16, L=24, k=3 in %.1f s" % (n, dt)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
+
+
+_ORIG_AFFINITY = None
+_JSON_FD = None
+
+
+def emit_json(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
+def bind_to_gpu_numa_node(local):
+    """Pin this rank to the CPUs next to its GPU (NVML's ideal affinity) BEFORE any pinned host buffer is allocated, so the
+    host-buffer (e2e) path copies over the local PCIe root and local DRAM.  ORION_B200_AFFINITY=0 disables it."""
+    if os.environ.get("ORION_B200_AFFINITY", "1") == "0":
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else local
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        global _ORIG_AFFINITY
+        _ORIG_AFFINITY = os.sched_getaffinity(0)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        cpus = sorted(os.sched_getaffinity(0))
+        return "%d cpus (%d-%d)" % (len(cpus), cpus[0], cpus[-1])
+    except Exception as e:                                        # not fatal: the benchmark runs unpinned
+        return "unavailable: %s" % (str(e)[:60],)
 
 
 def main():
@@ -134,6 +166,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-resnet", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON result: everything else a library prints there (NCCL's version banner under
+    # torchrun) is sent to stderr by pointing fd 1 at fd 2 for the duration of the run
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -143,6 +181,7 @@ def main():
         return
 
     os.environ.setdefault("ORION_B200_DEVICE", str(local))
+    affinity = bind_to_gpu_numa_node(local)
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
@@ -283,6 +322,8 @@ def main():
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline and world == 1:
+            if _ORIG_AFFINITY:
+                os.sched_setaffinity(0, _ORIG_AFFINITY)      # the CPU baseline gets every host core back (OpenMP starts its threads now)
             threads = os.cpu_count() or 1
             rate, n, dt = cpu_keyswitch_rate(threads)
             cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
@@ -295,7 +336,7 @@ def main():
                        "keyswitch_algorithmic_bytes": ks_bytes,
                        "keyswitch_hbm_floor_frac": (ks_bytes * total_ks / (ms * 1e-3) / 1e9 / world) / peak},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * 2 * LN * 8,
-                    "d2h_bytes_per_step": BATCH * 2 * LN * 8},
+                    "d2h_bytes_per_step": BATCH * 2 * LN * 8, "cpu_affinity": affinity},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "ntt2_ip_kernel<ArithF64> (second NTT pass of the digits fused with the evaluation-key inner product; %d limbs x %d ciphertexts per launch)" % (nf, GROUP),
                          "achieved": ip_gbs, "peak": peak, "unit": "GB/s", "frac": ip_gbs / peak,
@@ -314,7 +355,7 @@ def main():
             line["resnet20"] = resnet
         if lola:
             line["lola2"] = lola
-        print(json.dumps(line), flush=True)
+        emit_json(line)
     if world > 1:
         dist.destroy_process_group()
 
