@@ -30,10 +30,15 @@ typedef std::complex<double> cd;
 typedef std::map<int, std::vector<cd>> DiagMat;       // rotation -> diagonal (length n)
 
 constexpr int TPB = 256;
-constexpr int CHEB_DEPTH = 6, LOG_MSG_RATIO = 10;
+constexpr int LOG_MSG_RATIO = 10;
 // levels (= merged DFT factor matrices) spent on CoeffsToSlots / SlotsToCoeffs; ORION_B200_CTS_DEPTH / _STC_DEPTH override
 static int env_depth(const char* name, int dflt) { const char* s = std::getenv(name); const int v = s ? std::atoi(s) : dflt; return v >= 1 && v <= 8 ? v : dflt; }
 static const int CTS_DEPTH = env_depth("ORION_B200_CTS_DEPTH", 4), STC_DEPTH = env_depth("ORION_B200_STC_DEPTH", 3);
+// EvalMod: Chebyshev interpolant of degree 2^CHEB_DEPTH - 1 on an argument range of at most CHEB_RANGE radians, then r
+// double-angle steps.  Depth 6 (degree 63, 27 rad) or depth 5 (degree 31, 13.5 rad, one more double-angle step): the same
+// number of levels; ORION_B200_CHEB_DEPTH overrides.
+static const int CHEB_DEPTH = std::min(6, std::max(5, env_depth("ORION_B200_CHEB_DEPTH", 6)));
+static const double CHEB_RANGE = CHEB_DEPTH == 6 ? 27.0 : 13.5;
 
 // out[p][i][x] = centred(in[p][x] mod q0) mod q_i      (coefficient domain)
 __global__ void __launch_bounds__(TPB)
@@ -169,7 +174,7 @@ void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
     const int K = (int)std::ceil(8.0 * std::sqrt((double)h / 12.0));
     b->K1 = K + 1;
     b->r = 3;
-    while (2.0 * 3.14159265358979 * b->K1 / (double)(1 << b->r) > 27.0) ++b->r;
+    while (2.0 * 3.14159265358979 * b->K1 / (double)(1 << b->r) > CHEB_RANGE) ++b->r;
     const int logd = (int)std::lround(std::log2((double)s.default_scale));
     const int stc_bits = std::max(39, std::min(56, logd + 12));
     std::vector<u64> Q(s.ctx->mod.begin(), s.ctx->mod.begin() + s.nQ), used = s.ctx->mod, P;
@@ -194,7 +199,7 @@ void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
     b->cts_m = dft_factors(log_slots, 2 * s.N, CTS_DEPTH, true, roots);
     b->stc_m = dft_factors(log_slots, 2 * s.N, STC_DEPTH, false, roots);
     b->cheb.chebyshev = true;
-    b->cheb.coeffs = cheb_interp(63, (double)b->K1, b->r);
+    b->cheb.coeffs = cheb_interp((1 << CHEB_DEPTH) - 1, (double)b->K1, b->r);
     // X^(N/2): i in every slot
     std::vector<double2> iv(1 << bs.log_max_slots, make_double2(0.0, 1.0));
     b->times_i = bs.encode_complex(iv.data(), (int)iv.size(), b->top_level, 1, bs.log_max_slots);
@@ -328,13 +333,33 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
     bs.mul_int(im, -1, im);                                                  //      ->  u_im / K'
 
     // ---- EvalMod on both halves ----
+    // ORION_B200_BOOT_DEBUG=1: decrypt the EvalMod intermediates (the bootstrapping scheme holds the secret key) and print
+    // their distance from the exact function of the decrypted input -- where the precision of a circuit variant goes
+    static const bool boot_debug = std::getenv("ORION_B200_BOOT_DEBUG") != nullptr;
+    auto dbg_vals = [&](const Ciphertext& c) { auto p = bs.decrypt(c); return bs.decode(*p); };
     auto eval_mod = [&](const Ciphertext& x) {
+        std::vector<double2> xin;
+        if (boot_debug) xin = dbg_vals(x);
+        auto report = [&](const char* what, int k, const Ciphertext& c) {
+            if (!boot_debug) return;
+            std::vector<double2> v = dbg_vals(c);
+            double worst = 0, worst_im = 0, xmax = 0;
+            for (size_t i = 0; i < v.size(); ++i) {
+                const double want = std::cos(2.0 * PI * ((double)b.K1 * xin[i].x - 0.25) / (double)(1 << (b.r - k)));
+                worst = std::max(worst, std::fabs(v[i].x - want)); worst_im = std::max(worst_im, std::fabs(v[i].y));
+                xmax = std::max(xmax, std::fabs(xin[i].x));
+            }
+            std::fprintf(stderr, "[boot] %s %d: level %d, log2 scale %.3f, max |err| %.3e, max |imag| %.3e, max |x| %.4f\n", what, k,
+                         c.level, (double)std::log2((double)c.scale), worst, worst_im, xmax);
+        };
         auto y = poly_evaluate(bs, x, b.cheb, s_cheb);
+        report("chebyshev", 0, *y);
         for (int k = 0; k < b.r; ++k) {
             Ciphertext sq;
             bs.mul_relin(*y, *y, sq);
             bs.lin_comb_int({&sq}, {2.0L}, -roundl(sq.scale), sq.level, sq.scale, sq);      // 2 c^2 - 1 in one launch
             bs.rescale(sq, *y);
+            report("double-angle", k + 1, *y);
         }
         return y;
     };
