@@ -73,3 +73,31 @@ def test_binding_marshalling_shapes():
     assert len(_flat_argtypes(SCHEME_SIGNATURES["NewScheme"][0])) == 10
     assert len(_flat_argtypes(SCHEME_SIGNATURES["GenerateLinearTransform"][0])) == 7
     assert len(_flat_argtypes(SCHEME_SIGNATURES["Encode"][0])) == 4
+
+
+def test_reference_gpu_shim_loads_and_exports(orc):
+    """oracle/_ref/libgpuntt_refgpu.so (the reference's GPU merge NTT compiled in place for sm_100a): loads without a GPU
+    and exports the four entry points tests/test_gpu_refgpu.py drives.  Skipped when the reference tree was not there to
+    build it from."""
+    import pytest
+    R = orc.ref_gpu()
+    if R is None:
+        pytest.skip("oracle/_ref/libgpuntt_refgpu.so not built")
+    for name in ("refgpu_create", "refgpu_destroy", "refgpu_ntt_host", "refgpu_time_ms"):
+        assert hasattr(R, name)
+
+
+def test_bench_reference_arm_prints_exactly_one_json_line():
+    """`bench.py --impl reference` (the driver's reference arm): the CPU oracle on the host cores, one JSON line on stdout,
+    the keys of the contract, nothing else on stdout."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "keyswitches_per_s_logN16" and d["unit"] == "keyswitch/s"
+    assert d["value"] > 0 and d["higher_is_better"] is True
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
