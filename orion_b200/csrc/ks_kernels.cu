@@ -114,7 +114,8 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     ulonglong2* s_inv = (ulonglong2*)(s_sqd + ns + (ns & 1));   // [ns], 16-byte aligned
     int* s_off = (int*)(s_inv + ns);                   // [chunk]
     const bool f64 = !CENTERED && d.f64_src;
-    const int mm = d.mm;                               // this conversion's accumulation mode (CTA-uniform), at most MM
+    const int mm = d.mm & 3;                           // this conversion's accumulation mode (CTA-uniform), at most MM
+    const bool w32_ok = (d.mm & 4) != 0;               // 96-bit products for destinations below 2^32 (ORION_B200_BC_W32=0 disables)
     for (int i = threadIdx.x; i < ns * ndc; i += BC_TPB) {
         const int r = i / ndc, t = i - r * ndc;
         s_mat[r * chunk + t] = d.mat[r * nd + t0 + t]; s_matd[r * chunk + t] = d.mat_d[r * nd + t0 + t];
@@ -202,17 +203,31 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
             u64 hi[VEC], lo[VEC];
 #pragma unroll
             for (int c = 0; c < VEC; ++c) hi[c] = lo[c] = 0;
+            // destination below 2^32 (and raw accumulation allowed): the Montgomery-form matrix word is the 32-bit operand of
+            // a 96-bit product, whatever the size of the sources (ModDown from 61-bit special primes onto 30-bit limbs,
+            // ModUp digits that mix a 60-bit and 30-bit primes)
+            const bool w32 = MM >= 1 && mm >= 1 && w32_ok && (q >> 32) == 0;
+            if (w32 && !(MM == 2 && mm == 2)) {
 #pragma unroll
-            for (int i = 0; i < NS; ++i)
-                if (i < ns) {
-                    const u64 w = s_mat[i * chunk + t];
+                for (int i = 0; i < NS; ++i)
+                    if (i < ns) {
+                        const uint32_t w = (uint32_t)s_mat[i * chunk + t];
 #pragma unroll
-                    for (int c = 0; c < VEC; ++c) {
-                        if (MM == 2 && mm == 2) mac96_raw(hi[c], lo[c], (uint32_t)y[c][i], w);
-                        else if ((MM >= 1 && mm >= 1) || NS <= 3) mac128_raw(hi[c], lo[c], y[c][i], w);
-                        else mac128(hi[c], lo[c], y[c][i], w, q);
+                        for (int c = 0; c < VEC; ++c) mac96_raw(hi[c], lo[c], w, y[c][i]);
                     }
-                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < NS; ++i)
+                    if (i < ns) {
+                        const u64 w = s_mat[i * chunk + t];
+#pragma unroll
+                        for (int c = 0; c < VEC; ++c) {
+                            if (MM == 2 && mm == 2) mac96_raw(hi[c], lo[c], (uint32_t)y[c][i], w);
+                            else if ((MM >= 1 && mm >= 1) || NS <= 3) mac128_raw(hi[c], lo[c], y[c][i], w);
+                            else mac128(hi[c], lo[c], y[c][i], w, q);
+                        }
+                    }
+            }
             const u64 qi = s_dqi[t];
 #pragma unroll
             for (int c = 0; c < VEC; ++c) {
@@ -379,8 +394,10 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
         unsigned __int128 qsum = 0;
         bool small = true;
         for (int i : bc.h_src) { qsum += c.mod[i]; small = small && c.mod[i] < (1ull << 32); }
-        h[z].mm = qsum <= ((unsigned __int128)1 << 64) ? (small ? 2 : 1) : 0;
-        b.mac_mode = std::max(b.mac_mode, h[z].mm);
+        static const bool w32 = !(std::getenv("ORION_B200_BC_W32") && std::atoi(std::getenv("ORION_B200_BC_W32")) == 0);
+        const int mm = qsum <= ((unsigned __int128)1 << 64) ? (small ? 2 : 1) : 0;
+        h[z].mm = mm | (w32 ? 4 : 0);
+        b.mac_mode = std::max(b.mac_mode, mm);
     }
     auto buf = std::make_unique<DevBuf>(h.size() * sizeof(BcDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, h.data(), h.size() * sizeof(BcDev), cudaMemcpyHostToDevice, stream()));
