@@ -115,3 +115,56 @@ def test_dataflow_lanes_give_the_single_stream_result(b200lib, name):
     b = _replay_in_subprocess(name, {"ORION_B200_ASYNC": "0"})
     c = _replay_in_subprocess(name, {"ORION_B200_ASYNC": "1", "ORION_B200_STREAMS": "0"})
     assert a == b == c
+
+
+class _Tap:
+    """Forwards every backend call; keeps the words of the ciphertext handed to Decrypt (the replay's output ciphertext)."""
+
+    def __init__(self, backend, export):
+        self._b, self._export, self.last_words = backend, export, None
+
+    def __getattr__(self, name):
+        return getattr(self._b, name)
+
+    def Decrypt(self, ct):
+        self.last_words = self._export(ct)
+        return self._b.Decrypt(ct)
+
+
+@pytest.mark.parametrize("name", ["mlp", "lola"])
+def test_output_ciphertext_equals_the_oracles(b200lib, orc, name):
+    """the WHOLE encrypted inference (reference call sequence: 3 hoisted-BSGS linear transforms,
+    hybrid output rotations, 2 ciphertext products with relinearisation, rescales, bias additions) replayed on the GPU and
+    on the CPU oracle with the same seed -- the output ciphertexts are equal word for word, and so are the decoded logits."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle_backend import OracleBackend
+    from orion_b200.bindings import B200Library
+    from orion_b200.replay import Replayer, Trace
+    t = Trace(os.path.join(GOLD, "trace_%s.json" % name), os.path.join(GOLD, "trace_%s.npz" % name))
+    logN = t.meta["config"]["ckks_params"]["LogN"]
+
+    B = B200Library()
+    B.B200_SetSeed(42)
+
+    def export(ct):
+        level, deg = B.GetCiphertextLevel(ct), B.GetCiphertextDegree(ct)
+        out = np.empty((deg + 1, level + 1, 1 << logN), dtype=np.uint64)
+        B.B200_ExportCiphertext(ct, out)
+        return out
+
+    gpu = _Tap(B, export)
+    rg = Replayer(gpu, t, seed=1234)
+    rg.setup()
+    out_gpu = rg.infer()
+    B.DeleteScheme()
+
+    O = OracleBackend(42)
+    cpu = _Tap(O, lambda ct: O.words(ct).copy())
+    ro = Replayer(cpu, t, seed=1234)
+    ro.setup()
+    out_cpu = ro.infer()
+
+    assert gpu.last_words is not None and gpu.last_words.shape == cpu.last_words.shape
+    assert np.array_equal(gpu.last_words, cpu.last_words), "output ciphertext differs between GPU and oracle"
+    assert np.array_equal(np.asarray(out_gpu, dtype=np.float32), np.asarray(out_cpu, dtype=np.float32))

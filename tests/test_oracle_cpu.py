@@ -189,3 +189,24 @@ def test_encode_decode_roundtrip_and_sampling(orc):
     assert abs(g.mean()) < 0.05 and abs(g.std() - 3.2) < 0.05 and np.abs(g).max() <= 19
     u = S._uniform([0], 3)[0]
     assert u.max() < S.Q[0] and abs(float(u.mean()) / S.Q[0] - 0.5) < 0.02
+
+
+def test_mlp_and_lola_traces_on_the_oracle_match_cleartext():
+    """BASELINE.json configs[0] ("MLP (configs/mlp.yml) ... runs without a GPU"): the reference's exact backend-call sequence
+    for the MLP and for LoLA, replayed on the CPU oracle alone (tests/oracle_backend.py), passes the reference's own gate
+    (tests/models/test_mlp.py:45-48: MAE(clear, FHE) < 0.005) with the right argmax."""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, here)
+    from oracle_backend import OracleBackend
+    from orion_b200.replay import Replayer, Trace
+    for name in ("mlp", "lola"):
+        t = Trace(os.path.join(here, "golden", "trace_%s.json" % name), os.path.join(here, "golden", "trace_%s.npz" % name))
+        r = Replayer(OracleBackend(42), t, seed=1234)
+        r.setup()
+        out = r.infer()
+        clear = np.array(t.meta["clear_output"])
+        fhe = out[: len(clear)]
+        assert float(np.mean(np.abs(clear - fhe))) < 0.005, name
+        assert int(np.argmax(fhe)) == int(np.argmax(clear)), name
