@@ -1,4 +1,4 @@
-"""Debug helper (not a test): replay a trace on the GPU and on the oracle in lockstep; print the first op whose result differs.
+"""Debug helper (not a test): replay a trace on the GPU and on the oracle in lockstep; print the first op whose result differs."""
 import os, sys
 import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
