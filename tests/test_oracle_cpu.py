@@ -210,3 +210,22 @@ def test_mlp_and_lola_traces_on_the_oracle_match_cleartext():
         fhe = out[: len(clear)]
         assert float(np.mean(np.abs(clear - fhe))) < 0.005, name
         assert int(np.argmax(fhe)) == int(np.argmax(clear)), name
+
+
+def test_recorded_traces_mean_what_the_replay_assumes():
+    """The MLP and LoLA traces replayed on plain float vectors (tests/clear_backend.py: linear transform = sum_d diag_d *
+    roll(x, -d), rotation by r = roll(x, -r), products, additions) reproduce the cleartext logits the reference recorded
+    next to the trace -- the call-sequence semantics every encrypted replay in this suite relies on."""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, here)
+    from clear_backend import ClearBackend
+    from orion_b200.replay import Replayer, Trace
+    for name in ("mlp", "lola"):
+        t = Trace(os.path.join(here, "golden", "trace_%s.json" % name), os.path.join(here, "golden", "trace_%s.npz" % name))
+        r = Replayer(ClearBackend(), t, seed=1234)
+        r.setup()
+        out = r.infer()
+        clear = np.array(t.meta["clear_output"])
+        assert np.max(np.abs(out[: len(clear)] - clear)) < 1e-5, name
