@@ -404,3 +404,107 @@ class OScheme:
             out = (t0, t1) if out is None else (self._ew("add", out[0], t0, mods), self._ew("add", out[1], t1, mods))
         res = np.stack([self.ctx.moddown(level, out[0]), self.ctx.moddown(level, out[1])])
         return OCt(res, level, ct.scale * lt["scale"], ct.log_slots)
+
+    # ---- polynomial evaluation (orion/backend/lattigo/polyeval.go:63-84 contract; restates the product's own algorithm,
+    #      orion_b200/csrc/polyeval.cu: Paterson-Stockmeyer with backward scale propagation).  Checked on the CPU against
+    #      numpy (tests/test_oracle_cpu.py) and word for word against the GPU (tests/test_gpu_scheme.py). ----
+    def lin_comb_int(self, ops, ks, c0, level, S):
+        """sum_i k_i * a_i + c0 at `level`, declared scale S; k_i, c0 integers carried as long doubles."""
+        L = level + 1
+        mods = list(range(L))
+        polys = ops[0].degree + 1
+        acc = None
+        for a, k in zip(ops, ks):
+            k = LD(k)
+            sc = self._const_rns(-1.0 if k < 0 else 1.0, abs(k), mods)
+            term = [self._mul_scalar(a.data[p][:L], sc, mods) for p in range(polys)]
+            acc = term if acc is None else [self._ew("add", acc[p], term[p], mods) for p in range(polys)]
+        c0 = LD(c0)
+        if c0 != 0:
+            acc[0] = self._add_scalar(acc[0], self._const_rns(-1.0 if c0 < 0 else 1.0, abs(c0), mods), mods)
+        return OCt(np.stack(acc), level, S, ops[0].log_slots, polys - 1)
+
+    def lin_comb_scaled(self, ops, cs, c0, level, S):
+        S = LD(S)
+        ks = []
+        for a, c in zip(ops, cs):
+            v = np.round(abs(LD(c) * (S / a.scale)))
+            ks.append(-v if c < 0 else v)
+        v0 = np.round(abs(LD(c0) * S))
+        return self.lin_comb_int(ops, ks, -v0 if c0 < 0 else v0, level, S)
+
+    def poly_evaluate(self, ct, coeffs, chebyshev, out_scale):
+        def bitlen(x):
+            return int(x).bit_length()
+        p = [float(np.float32(c)) for c in coeffs]
+        d = len(p) - 1
+        while d > 0 and p[d] == 0.0:
+            d -= 1
+        depth, in_level = bitlen(d), ct.level
+        out_level = in_level - depth
+        assert d >= 1 and out_level >= 0
+        B = 1 << ((depth + 1) // 2)
+        P = {1: ct.copy()}
+        q_at = lambda l: LD(self.Q[l])
+
+        def power(n):
+            if n in P:
+                return P[n]
+            a = 1 << (bitlen(n - 1) - 1)
+            b = n - a
+            A, Bc = power(a), power(b)
+            prod = self.mul_relin(A, Bc)
+            if chebyshev:
+                c = a - b
+                if c == 0:
+                    prod = self.lin_comb_int([prod], [LD(2)], -np.round(prod.scale), prod.level, prod.scale)
+                else:
+                    Cc = power(c)
+                    k = np.round(prod.scale / Cc.scale)
+                    prod = self.lin_comb_int([prod, Cc], [LD(2), -k], LD(0), prod.level, prod.scale)
+            P[n] = self.rescale(prod)
+            return P[n]
+
+        level_of = lambda n: in_level - (0 if n <= 1 else bitlen(n - 1))
+        in_basis = lambda n: n < B or (n & (n - 1)) == 0
+
+        def E(p, L, S):
+            S = LD(S)
+            deg = len(p) - 1
+            while deg > 0 and p[deg] == 0.0:
+                deg -= 1
+            direct = all(p[i] == 0.0 or (in_basis(i) and level_of(i) >= L) for i in range(1, deg + 1))
+            if direct:
+                ops = [power(i) for i in range(1, deg + 1) if p[i] != 0.0]
+                cs = [p[i] for i in range(1, deg + 1) if p[i] != 0.0]
+                assert ops, "constant polynomials are not staged in the oracle"
+                return self.lin_comb_scaled(ops, cs, p[0], L, S)
+            assert deg >= 2
+            g = 1 << (bitlen(deg) - 1)
+            q = [0.0] * (deg - g + 1)
+            r = list(p[:g])
+            if chebyshev:
+                q[0] = p[g]
+                for k in range(1, deg - g + 1):
+                    q[k] = 2.0 * p[g + k]
+                    r[g - k] -= p[g + k]
+            else:
+                for k in range(deg - g + 1):
+                    q[k] = p[g + k]
+            Pg = power(g)
+            usePg = self.drop_level(Pg, L) if Pg.level > L else Pg
+            if deg == g:
+                res = self.mul_const_scaled(usePg, q[0], S / Pg.scale)
+            else:
+                qS = (S / Pg.scale) * q_at(L + 1)
+                A = self.rescale(E(q, L + 1, qS))
+                A.scale = S / Pg.scale
+                res = self.mul_relin(A, usePg)
+            res.scale = S
+            if any(v != 0.0 for v in r):
+                res = self.add(res, E(r, L, S))
+            return res
+
+        res = self.rescale(E(p[: d + 1], out_level + 1, LD(out_scale) * q_at(out_level + 1)))
+        res.scale = LD(out_scale)
+        return res

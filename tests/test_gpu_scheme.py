@@ -270,3 +270,33 @@ def test_bootstrap(orc, b200lib, num_slots):
     assert np.max(np.abs(re - x * x)) < 5e-4
     B.DeleteBootstrappers()
     B.DeleteScheme()
+
+
+def test_polynomial_evaluation_words_equal_the_oracles(orc, b200lib):
+    """a13, word for word: EvaluatePolynomial (Chebyshev and monomial, degrees 5-31: power basis, Paterson-Stockmeyer
+    recursion with backward scale propagation, relinearisations, rescales) gives the ciphertext oracle/scheme.py
+    poly_evaluate computes on the CPU from the same input ciphertext."""
+    from oracle.scheme import OScheme
+    from orion_b200.bindings import B200Library
+    logn, logq, logp, logscale, h, seed = 12, [50] + [40] * 7, [56, 56], 40, 64, 7
+    B = B200Library()
+    B.B200_SetSeed(seed)
+    B.NewScheme(logn, logq, logp, logscale, h, "standard", "", "none")
+    try:
+        B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey()
+        B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor(); B.NewPolynomialEvaluator()
+        O = OScheme(logn, logq, logp, logscale, h, seed)
+        O.gen_secret_key(); O.gen_public_key(); O.gen_relin_key()
+        rng = np.random.default_rng(1)
+        x = rng.uniform(-1, 1, 1 << (logn - 1)).astype(np.float32)
+        ct = B.Encrypt(B.Encode(x.tolist(), 7, 1 << logscale))
+        oct_ = O.encrypt(O.encode(x.astype(np.float64), 7, 2.0 ** logscale))
+        assert np.array_equal(export_ct(B, O, ct), oct_.data)
+        for deg, cheb in ((7, True), (15, True), (27, True), (31, True), (5, False)):
+            c = (rng.uniform(-1, 1, deg + 1) / (1 if cheb else deg)).astype(np.float32)
+            poly = B.GenerateChebyshev(c.tolist()) if cheb else B.GenerateMonomial(c.tolist())
+            got = export_ct(B, O, B.EvaluatePolynomial(ct, poly, 1 << logscale))
+            want = O.poly_evaluate(oct_, c, cheb, 2.0 ** logscale).data
+            assert got.shape == want.shape and np.array_equal(got, want), (deg, cheb)
+    finally:
+        B.DeleteScheme()

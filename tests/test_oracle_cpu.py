@@ -229,3 +229,24 @@ def test_recorded_traces_mean_what_the_replay_assumes():
         out = r.infer()
         clear = np.array(t.meta["clear_output"])
         assert np.max(np.abs(out[: len(clear)] - clear)) < 1e-5, name
+
+
+def test_oracle_polynomial_evaluation_matches_numpy(orc):
+    """a13 on the oracle (oracle/scheme.py poly_evaluate restates csrc/polyeval.cu; the word-for-word comparison with the
+    GPU is tests/test_gpu_scheme.py::test_polynomial_evaluation_words_equal_the_oracles).
+    Contract of LG/polyeval.go:63-84: output level = input level - ceil(log2(d+1)), output scale exactly the requested one,
+    values = the polynomial of the slots (tolerance 1e-6 at a 2^40 scale)."""
+    from numpy.polynomial import chebyshev as C
+    from oracle.scheme import OScheme
+    O = OScheme(12, [50] + [40] * 7, [56, 56], 40, 64, 7)
+    O.gen_secret_key(); O.gen_public_key(); O.gen_relin_key()
+    rng = np.random.default_rng(1)
+    x = rng.uniform(-1, 1, 2048)
+    ct = O.encrypt(O.encode(x, 7, 2.0 ** 40))
+    for deg, cheb in ((7, True), (15, True), (27, True), (31, True), (5, False)):
+        c = (rng.uniform(-1, 1, deg + 1) / (1 if cheb else deg)).astype(np.float32)
+        out = O.poly_evaluate(ct, c, cheb, 2.0 ** 40)
+        assert out.level == 7 - int(deg).bit_length() and out.scale == 2.0 ** 40
+        got = np.real(O.decode(O.decrypt(out)))
+        want = C.chebval(x, c.astype(np.float64)) if cheb else np.polynomial.polynomial.polyval(x, c.astype(np.float64))
+        assert np.max(np.abs(got - want)) < 1e-6, (deg, cheb)
