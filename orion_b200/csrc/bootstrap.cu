@@ -14,7 +14,8 @@
 //             hold u/(2K'), u = phase_j/q0; real / imaginary parts split with one conjugation
 //   EvalMod : sin(2 pi u) = cos(2 pi (u - 1/4)): degree-63 Chebyshev interpolant of cos(2 pi (K' x - 1/4) / 2^r)
 //             followed by r double-angle steps c <- 2c^2 - 1
-//   StC     : 3 transforms = the forward special FFT without bit-reversal, scaled by q0/(2 pi k scale); the last
+//   StC     : 3 transforms = the forward special FFT without bit-reversal, scaled by g q0/(2 pi k scale), g = MaxSlots/slots
+//             (the shim's post-factor, LG/bootstrapper.go:73-74: a zero-padded input x comes back as replicate(x)); the last
 //             plaintext scale is chosen so that the output scale is exactly the default scale.
 #include "bootstrap.h"
 #include "lintrans.h"
@@ -189,7 +190,7 @@ void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
     for (int bits : logP) np[bits]++;
     for (auto& kv : np) take(kv.first, kv.second, P);
     OB_CHECK(!P.empty(), "NewBootstrapper: boot_params.LogP is empty");
-    b->bs = std::make_unique<Scheme>(s.ctx->logN, Q, P, s.params.log_scale, s.params.h, s.seed ^ 0xB007B007ull ^ (u64)num_slots);
+    b->bs = std::make_unique<Scheme>(s.ctx->logN, Q, P, s.params.log_scale, s.params.h, s.rng.derive(0xB007B007ull ^ (u64)num_slots));
     Scheme& bs = *b->bs;
     bs.default_scale = s.default_scale;
     bs.set_secret_key(s.sk_coeffs);
@@ -301,7 +302,10 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
         // EvalMod output scale (tracked exactly below) -> StC plaintext scales so that the result has the default scale
         scale_t s_out = s_cheb;
         for (int k = 0; k < b.r; ++k) s_out = s_out * s_out / bs.q_at(lvl_after_cts - CHEB_DEPTH - k);
-        const double mu = (double)((long double)q0 / (2.0L * PI * (long double)eff));
+        // The Go shim multiplies Lattigo's output by 2^(LogMaxSlots - LogSlots) (LG/bootstrapper.go:73-74): Orion hands over a
+        // ZERO-PADDED full-slot vector (orion/nn/operations.py:59-60,85-87), whose projection onto the slot subring is
+        // replicate(x)/g, and expects replicate(x) back.  The factor g is folded into SlotsToCoeffs (no extra level).
+        const double mu = (double)((long double)q0 / (2.0L * PI * (long double)eff)) * g;
         const double f_stc = std::pow(mu, 1.0 / stc_groups);
         const scale_t target = s.default_scale;
         const long double per = powl((long double)(target / s_out), 1.0L / stc_groups);

@@ -182,12 +182,13 @@ void NewScheme(int logN, int* logQ, int lenQ, int* logP, int lenP, int logScale,
     std::string rt = ringType ? ringType : "standard";
     for (auto& ch : rt) ch = (char)std::tolower(ch);
     p.conjugate_invariant = (rt != "standard");
-    u64 seed = g_seed;
-    if (!g_seed_set) { std::random_device rd; seed = ((u64)rd() << 32) ^ rd(); }   // OS randomness, as Lattigo does
+    // default: ChaCha20 keyed with 2 x 256 bits of OS randomness (Lattigo: blake2b XOF keyed from crypto/rand);
+    // B200_SetSeed switches to the oracle's invertible test generator -- parity tests only
+    const SchemeRng rng = g_seed_set ? SchemeRng::test_mode(g_seed) : SchemeRng::from_os();
     settle_all();
     lt_reset(); poly_reset(); boot_reset();
     g_scheme.reset();
-    g_scheme = std::make_unique<Scheme>(p, seed);
+    g_scheme = std::make_unique<Scheme>(p, rng);
 }
 void DeleteScheme(void) {
     settle_all();

@@ -40,7 +40,7 @@ pk_assemble_kernel(const u64* __restrict__ a, const u64* __restrict__ e, const u
 }
 }  // namespace
 
-Scheme::Scheme(const SchemeParams& p, u64 seed_) : params(p) {
+Scheme::Scheme(const SchemeParams& p, const SchemeRng& rng_) : params(p) {
     // RingType ConjugateInvariant (configs/lola.yml; LG/scheme.go:46-55): Lattigo folds Z[X+X^-1]/(X^2N+1) into N
     // coefficients, N real slots, primes = 1 mod 4N.  This backend serves it with the standard ring of degree 2N: the
     // same prime chain (NthRoot 4N), the same N slots (orion/backend/python/parameters.py:33-35), every operation
@@ -49,20 +49,20 @@ Scheme::Scheme(const SchemeParams& p, u64 seed_) : params(p) {
     std::vector<u64> Q, P;
     gen_moduli(p.logQ, p.logP, ring_logN + 1, Q, P);
     ctx = std::make_unique<Context>(ring_logN, Q, P);
-    init_common(seed_);
+    init_common(rng_);
 }
-Scheme::Scheme(int logN, const std::vector<u64>& Q, const std::vector<u64>& P, int log_scale, int h, u64 seed_) {
+Scheme::Scheme(int logN, const std::vector<u64>& Q, const std::vector<u64>& P, int log_scale, int h, const SchemeRng& rng_) {
     params.logN = logN; params.log_scale = log_scale; params.h = h;
     for (u64 q : Q) params.logQ.push_back(64 - __builtin_clzll(q));
     for (u64 q : P) params.logP.push_back(64 - __builtin_clzll(q));
     ctx = std::make_unique<Context>(logN, Q, P);
-    init_common(seed_);
+    init_common(rng_);
 }
-void Scheme::init_common(u64 seed_) {
+void Scheme::init_common(const SchemeRng& rng_) {
     pev = std::make_unique<PolyEvaluator>(*ctx);
     N = ctx->N; nQ = ctx->nQ; nP = ctx->nP; max_level = nQ - 1; log_max_slots = ctx->logN - 1;
     default_scale = std::ldexp((scale_t)1, params.log_scale);
-    seed = seed_;
+    rng = rng_;
 }
 Scheme::~Scheme() {
     cudaStreamSynchronize(stream());
@@ -85,7 +85,7 @@ void Scheme::set_secret_key(const std::vector<int64_t>& coeffs) {
 }
 void Scheme::gen_secret_key() {
     std::vector<int64_t> s;
-    sample_ternary_hw_host(N, params.h, seed, new_event(), s);
+    sample_ternary_hw_host(N, params.h, rng.sec, new_event(), s);
     set_secret_key(s);
 }
 
@@ -107,8 +107,8 @@ void Scheme::gen_public_key() {
     pk.alloc(2 * W * 8);
     DevBuf small((size_t)N * 8), e(W * 8);
     u64* a = pk.u() + W;
-    sample_uniform(*ctx, a, full_chain(*ctx), seed, ev);
-    sample_gaussian(*ctx, small.as<int64_t>(), seed, ev + 512);
+    sample_uniform(*ctx, a, full_chain(*ctx), rng.pub, ev);
+    sample_gaussian(*ctx, small.as<int64_t>(), rng.sec, ev + 512);
     small_to_rns(*ctx, small.as<int64_t>(), e.u(), full_chain(*ctx));
     ntt_forward(*ctx, e.u(), e.u(), full_chain_plan(*ctx));
     dim3 grid(N / TPB, ctx->nmod);
@@ -127,8 +127,8 @@ std::unique_ptr<EvalKey> Scheme::gen_eval_key(const u64* sk_in, const u64* sk_ou
     const std::vector<int> mods = full_chain(*ctx);
     dim3 grid(N / TPB, nmod);
     for (int j = 0; j < beta; ++j) {
-        sample_uniform(*ctx, a.u(), mods, seed, ev + (u64)j * 128);
-        sample_gaussian(*ctx, small.as<int64_t>(), seed, ev + (u64)j * 128 + 64);
+        sample_uniform(*ctx, a.u(), mods, rng.pub, ev + (u64)j * 128);
+        sample_gaussian(*ctx, small.as<int64_t>(), rng.sec, ev + (u64)j * 128 + 64);
         small_to_rns(*ctx, small.as<int64_t>(), e.u(), mods);
         ntt_forward(*ctx, e.u(), e.u(), plan);
         const int lo = j * nP, hi = std::min((j + 1) * nP, nQ);
@@ -235,13 +235,13 @@ std::unique_ptr<Ciphertext> Scheme::encrypt(const Plaintext& pt) {
     const NttPlan plan = make_ntt_plan(*ctx, l);
     // u: ternary with the secret's Hamming weight
     std::vector<int64_t> uh;
-    sample_ternary_hw_host(N, params.h, seed, ev, uh);
+    sample_ternary_hw_host(N, params.h, rng.sec, ev, uh);
     DevBuf small((size_t)N * 8), u((size_t)W * N * 8), e((size_t)W * N * 8), acc((size_t)2 * W * N * 8);
     OB_CUDA(cudaMemcpyAsync(small.p, uh.data(), (size_t)N * 8, cudaMemcpyHostToDevice, stream()));
     small_to_rns(*ctx, small.as<int64_t>(), u.u(), mods);
     ntt_forward(*ctx, u.u(), u.u(), plan);
     for (int c = 0; c < 2; ++c) {
-        sample_gaussian(*ctx, small.as<int64_t>(), seed, ev + 1 + c);
+        sample_gaussian(*ctx, small.as<int64_t>(), rng.sec, ev + 1 + c);
         small_to_rns(*ctx, small.as<int64_t>(), e.u(), mods);
         ntt_forward(*ctx, e.u(), e.u(), plan);
         u64* a = acc.u() + (size_t)c * W * N;

@@ -61,9 +61,9 @@ struct SchemeParams {
 
 class Scheme {
   public:
-    Scheme(const SchemeParams& p, u64 seed);
+    Scheme(const SchemeParams& p, const SchemeRng& rng);
     // a scheme over an explicit chain sharing nothing with the parameter generator (bootstrapping contexts)
-    Scheme(int logN, const std::vector<u64>& Q, const std::vector<u64>& P, int log_scale, int h, u64 seed);
+    Scheme(int logN, const std::vector<u64>& Q, const std::vector<u64>& P, int log_scale, int h, const SchemeRng& rng);
     ~Scheme();
 
     SchemeParams params;
@@ -73,7 +73,7 @@ class Scheme {
     scale_t default_scale;
 
     // ---- randomness: every sampling event takes a fresh block of streams ----
-    u64 seed;
+    SchemeRng rng;                                       // see scheme_kernels.h: ChaCha20 from OS keys, or the oracle's test generator
     u64 next_event = 0;
     u64 new_event() { return (next_event++) * 16384ull; }
 
@@ -137,7 +137,7 @@ class Scheme {
     scale_t q_at(int level) const { return (scale_t)ctx->mod[level]; }
 
   private:
-    void init_common(u64 seed);
+    void init_common(const SchemeRng& rng);
     void match_scale(const Ciphertext& a, scale_t sa, const u64* b_data, int b_polys, int b_level, scale_t sb, int level,
                      Ciphertext& out, bool sub);
     void assign(Ciphertext& out, std::unique_ptr<Ciphertext> tmp);

@@ -4,6 +4,7 @@
 // float64 only, compiled with --fmad=false: every operation is a single IEEE op in a fixed order so that the
 // oracle (gcc -ffp-contract=off) reproduces the encodings bit for bit.
 #include "scheme_kernels.h"
+#include <random>
 #include <cmath>
 
 namespace ob {
@@ -21,21 +22,21 @@ __constant__ u64 c_gauss_cdt[20] = {
 
 __global__ void __launch_bounds__(TPB)
 uniform_kernel(u64* __restrict__ out, int N, const LimbDesc* __restrict__ limbs, const ModConst* __restrict__ mc,
-               u64 seed, u64 stream0) {
+               const Rng rng, u64 stream0) {
     OB_PDL_SYNC();
     const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x;
     const ModConst& m = mc[limbs[t].mod];
     const u64 q = m.q, mask = m.bits >= 64 ? ~0ull : ((1ull << m.bits) - 1);
     u64 r = 0; int a = 0;
-    for (; a < 64; ++a) { r = rng_u64(seed, stream0 + t, ((u64)a << 32) | (u64)x) & mask; if (r < q) break; }
+    for (; a < 64; ++a) { r = rng_u64(rng, stream0 + t, ((u64)a << 32) | (u64)x) & mask; if (r < q) break; }
     out[(size_t)t * N + x] = a < 64 ? r : r % q;
 }
 
 __global__ void __launch_bounds__(TPB)
-gaussian_kernel(int64_t* __restrict__ out, u64 seed, u64 stream) {
+gaussian_kernel(int64_t* __restrict__ out, const Rng rng, u64 stream) {
     OB_PDL_SYNC();
     const int x = blockIdx.x * TPB + threadIdx.x;
-    const u64 r = rng_u64(seed, stream, (u64)x), s = rng_u64(seed, stream, (1ull << 32) | (u64)x);
+    const u64 r = rng_u64(rng, stream, (u64)x), s = rng_u64(rng, stream, (1ull << 32) | (u64)x);
     int k = 0;
     while (r > c_gauss_cdt[k]) ++k;
     out[x] = (s & 1) ? -(int64_t)k : (int64_t)k;
@@ -188,14 +189,30 @@ const LimbDesc* mods_list(Context& c, const std::vector<int>& mods) {
 
 }  // namespace
 
-void sample_uniform(Context& c, u64* out, const std::vector<int>& mods, u64 seed, u64 stream0) {
+void sample_uniform(Context& c, u64* out, const std::vector<int>& mods, const Rng& rng, u64 stream0) {
     dim3 grid(c.N / TPB, (unsigned)mods.size());
-    OB_LAUNCH(uniform_kernel, grid, TPB, 0, stream(), out, c.N, mods_list(c, mods), c.dmc(), seed, stream0);
+    OB_LAUNCH(uniform_kernel, grid, TPB, 0, stream(), out, c.N, mods_list(c, mods), c.dmc(), rng, stream0);
 }
-void sample_gaussian(Context& c, int64_t* out, u64 seed, u64 strm) {
-    OB_LAUNCH(gaussian_kernel, c.N / TPB, TPB, 0, stream(), out, seed, strm);
+void sample_gaussian(Context& c, int64_t* out, const Rng& rng, u64 strm) {
+    OB_LAUNCH(gaussian_kernel, c.N / TPB, TPB, 0, stream(), out, rng, strm);
 }
-void sample_ternary_hw_host(int N, int h, u64 seed, u64 strm, std::vector<int64_t>& out) {
+SchemeRng SchemeRng::test_mode(u64 seed) {
+    SchemeRng r; r.pub.seed = r.sec.seed = seed; return r;
+}
+SchemeRng SchemeRng::from_os() {
+    SchemeRng r;
+    std::random_device rd;                        // /dev/urandom or RDRAND in libstdc++
+    for (Rng* g : {&r.pub, &r.sec}) {
+        g->chacha = 1;
+        for (uint32_t& w : g->key) w = (uint32_t)rd();
+    }
+    return r;
+}
+SchemeRng SchemeRng::derive(u64 tweak) const {
+    if (pub.chacha) return from_os();
+    return test_mode(pub.seed ^ tweak);
+}
+void sample_ternary_hw_host(int N, int h, const Rng& seed, u64 strm, std::vector<int64_t>& out) {
     std::vector<int> pos(N);
     out.assign(N, 0);
     for (int i = 0; i < N; ++i) pos[i] = i;

@@ -73,8 +73,9 @@ def _composite(degrees, logalpha):
         c, err = _remez_odd_one(a, b, d)
         c = np.concatenate([c, np.zeros(degrees[i] - d)])
         if i < len(degrees) - 1:
-            c = c / (1.0 + err)                      # keep the range inside [-1, 1] for the next stage
-            a, b = (1.0 - err) / (1.0 + err), 1.0
+            top = (1.0 + err) * (1.0 + 1e-6)         # the error is measured on a grid: a 1e-6 margin keeps the true
+            c = c / top                              # range inside [-1, 1], the next stage's Chebyshev domain
+            a, b = (1.0 - err) / top, 1.0
         polys.append(c)
     return polys
 

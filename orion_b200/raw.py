@@ -166,6 +166,20 @@ class RawContext:
                                      arr(*evk_devs), arr(*[o.ctypes.data for o in outs]))
         return outs
 
+    def keyswitch_batch_dev(self, level, cts, evk_devs, has_c0=True):
+        """Device-resident batch entry point (what bench.py times): one launch sequence for all ciphertexts.
+        cts: [n][2][L][N] (c0, c1) if has_c0 else [n][L][N]; returns [n][2][L][N]."""
+        cts = np.ascontiguousarray(cts, dtype=np.uint64)
+        n = cts.shape[0]
+        assert cts.size == n * (2 if has_c0 else 1) * (level + 1) * self.N
+        out = np.empty((n, 2, level + 1, self.N), dtype=np.uint64)
+        d_in, d_out = self.lib.B200_DevAlloc(cts.size), self.lib.B200_DevAlloc(out.size)
+        self.lib.B200_Upload(d_in, _p(cts), cts.size)
+        self.lib.B200_KeySwitchBatchDev(self.h, level, n, d_in, 1 if has_c0 else 0, (ctypes.c_void_p * n)(*evk_devs), d_out)
+        self.lib.B200_Download(_p(out), d_out, out.size)
+        self.lib.B200_DevFree(d_in); self.lib.B200_DevFree(d_out)
+        return out
+
     def decompose(self, level, c1):
         c1 = np.ascontiguousarray(c1, dtype=np.uint64).reshape(level + 1, self.N)
         out = np.empty((self.num_digits(level), level + 1 + self.nP, self.N), dtype=np.uint64)

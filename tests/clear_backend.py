@@ -20,7 +20,7 @@ class ClearBackend:
         self.slots, self.obj, self.next_id = None, {}, 0
 
     def NewScheme(self, logN, logQ, logP, logScale, h, ringType, keysPath, ioMode):
-        self.slots = 1 << (logN - 1)
+        self.slots = 1 << (logN - 1 if ringType.lower() == "standard" else logN)
 
     def __getattr__(self, name):                     # New*, Generate*Key*, Set*Scale, AddRotationKey, ...: nothing to do
         if name.startswith(("New", "Generate", "Set", "AddRotationKey", "Remove", "Load")):

@@ -227,8 +227,8 @@ class SymbolicBackend:
         idxs = sorted({k & (self.max_slots - 1) for k in self.lt[lt]["idxs"]})
         n1 = OScheme.find_best_bsgs_ratio(idxs, self.max_slots, 0)
         _, giants, babies = OScheme.bsgs_index(idxs, self.max_slots, n1)
-        two_n = 2 << self.logn
-        return sorted({pow(5, r, two_n) for r in giants + babies if r})
+        nth_root = 2 * self.max_slots * 2                   # 2N (standard ring) / 4N (conjugate-invariant ring: N slots)
+        return sorted({pow(5, r, nth_root) for r in giants + babies if r})
 
     def GenerateConsolidatedRotationKeys(self, keys):
         self._log("GenerateConsolidatedRotationKeys", [int(k) for k in keys])
@@ -310,7 +310,7 @@ def build_model(name):
 def main():
     import yaml
     name = sys.argv[1] if len(sys.argv) > 1 else "mlp"
-    keep = name != "resnet20" and "--structure-only" not in sys.argv
+    keep = "--structure-only" not in sys.argv
     stub_missing_modules()
     patch_scipy_for_torch_indices()
     sys.path.insert(0, REF)

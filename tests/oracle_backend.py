@@ -36,8 +36,10 @@ class OracleBackend:
 
     # ---- scheme / keys (LG/scheme.go:35-86, LG/keygenerator.go:13-35) ----
     def NewScheme(self, logN, logQ, logP, logScale, h, ringType, keysPath, ioMode):
-        assert ringType.lower() == "standard", "the oracle backend covers the Standard ring"
-        self.O = OScheme(logN, list(logQ), list(logP), logScale, h, self.seed)
+        # RingType ConjugateInvariant is served the way the product serves it (csrc/scheme.cu constructor): the standard
+        # ring of degree 2N over the same prime chain (primes = 1 mod 4N), N real slots
+        ci = ringType.lower() != "standard"
+        self.O = OScheme(logN + (1 if ci else 0), list(logQ), list(logP), logScale, h, self.seed)
 
     def GenerateSecretKey(self): self.O.gen_secret_key()
     def GeneratePublicKey(self): self.O.gen_public_key()

@@ -30,16 +30,43 @@ def test_mlp_encrypted_inference_matches_cleartext(b200lib):
     assert res["counts"]["EvaluateLinearTransform"] == 3 and res["counts"]["MulRelinCiphertextNew"] == 2
 
 
-def test_resnet20_trace_replays_with_bootstrapping(b200lib):
-    """ResNet-20 as shipped (configs/resnet.yml: logN=13, 33 Q-limbs, boot LogP 8x61): the reference's exact call
-    sequence (147 linear transforms, 138 polynomial evaluations, 28 bootstraps) on synthetic payloads of the recorded
-    shapes.  Checks the structural contract end to end: every op's level budget holds and the output is finite."""
+def clear_replay(name):
+    """The same trace on plain float64 slot vectors (tests/clear_backend.py): what the encrypted replay computes, in the clear."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from clear_backend import ClearBackend
+    from orion_b200.replay import Replayer, Trace
+    t = Trace(os.path.join(GOLD, "trace_%s.json" % name), os.path.join(GOLD, "trace_%s.npz" % name))
+    r = Replayer(ClearBackend(), t, seed=1234)
+    r.setup()
+    return np.asarray(r.infer(), dtype=np.float64)
+
+
+def test_resnet20_encrypted_inference_matches_cleartext(b200lib):
+    """ResNet-20 as shipped (configs/resnet.yml: logN=13, 33 Q-limbs, boot LogP 8x61), the reference's own example flow
+    (examples/run_resnet.py:19-60: default-init weights, orion.fit on the input, FHE output compared with the cleartext
+    output): the recorded call sequence with its REAL payloads -- 147 linear transforms, 138 polynomial evaluations (57
+    composite-sign / activation polynomials), 28 chained bootstraps.
+    Gates (CKKS tolerance, stated here):
+      * backend numerics: max |FHE - same call sequence evaluated in the clear| <= 1e-3 on the 10 logits (north star),
+      * the reference's end-to-end comparison against the exact cleartext network: same argmax, MAE < 0.02.  (The
+        polynomial ReLU itself -- minimax sign [15,15,27], alpha = 2^-6 -- deviates from the exact ReLU by up to 0.025 on
+        these logits in the clear as well: that is the model's approximation error, not the backend's.)"""
     res = run_trace("resnet20")
     c = res["counts"]
     assert c["EvaluateLinearTransform"] == 147 and c["EvaluatePolynomial"] == 138 and c["Bootstrap"] == 28
-    out = res["output"]
-    assert out is not None and np.all(np.isfinite(out))
-    print("resnet20 logN=13: setup %.1f s, one encrypted inference %.2f s" % (res["setup_s"], res["infer_s"]))
+    assert res["meta"]["payloads"] == "full"
+    clear = np.array(res["meta"]["clear_output"])
+    fhe = np.asarray(res["output"], dtype=np.float64)[: len(clear)]
+    same_ops_clear = clear_replay("resnet20")[: len(clear)]
+    assert np.all(np.isfinite(fhe))
+    err = float(np.max(np.abs(fhe - same_ops_clear)))
+    mae = float(np.mean(np.abs(fhe - clear)))
+    print("resnet20 logN=13: setup %.1f s, inference %.2f s, max|FHE - clear replay| %.2e, MAE vs exact network %.2e"
+          % (res["setup_s"], res["infer_s"], err, mae))
+    assert err <= 1e-3, (err, fhe, same_ops_clear)
+    assert int(np.argmax(fhe)) == int(np.argmax(clear)) == int(np.argmax(same_ops_clear))
+    assert mae < 0.02, (mae, fhe, clear)
 
 
 def test_lola_encrypted_inference_matches_cleartext(b200lib):

@@ -116,16 +116,89 @@ def test_keyswitch_stages_and_full(orc, b200lib, case):
         ref2 = ref.copy()
         ref2[0] = oc.elementwise("add", ref[0], c0)
         assert np.array_equal(out2, ref2)
-    # batched, pipelined host-buffer entry point: same results as one call per ciphertext
+    # batched entry points (pipelined host-buffer call and the device-resident call bench.py times): every output
+    # ciphertext equals the ORACLE's key switch of that ciphertext.  Under ORION_B200_FUSED_IP=1 (see
+    # test_fused_inner_product_switch_*) this is the route into ntt2_ip_kernel / ntt_forward_first / the raw-double
+    # ModUp hand-off for every chain in CASES.
     level = oc.nQ - 1
     cts = [np.stack([oc.uniform_poly(rng, list(range(level + 1))) for _ in range(2)]) for _ in range(5)]
+    refs = [oc.keyswitch(level, ct[1], evk) for ct in cts]
+    refs_c0 = []
+    for ct, r in zip(cts, refs):
+        r2 = r.copy(); r2[0] = oc.elementwise("add", r[0], ct[0]); refs_c0.append(r2)
     outs = gc.keyswitch_batch(level, cts, [evk_dev] * 5)
-    for ct, o in zip(cts, outs):
-        assert np.array_equal(o, gc.keyswitch(level, ct[1], evk_dev, c0=ct[0]))
+    for r, o in zip(refs_c0, outs):
+        assert np.array_equal(o, r)
     outs = gc.keyswitch_batch(level, [ct[1] for ct in cts], [evk_dev] * 5, has_c0=False)
-    for ct, o in zip(cts, outs):
-        assert np.array_equal(o, gc.keyswitch(level, ct[1], evk_dev))
+    for r, o in zip(refs, outs):
+        assert np.array_equal(o, r)
+    outs = gc.keyswitch_batch_dev(level, np.stack(cts), [evk_dev] * 5)
+    for r, o in zip(refs_c0, outs):
+        assert np.array_equal(o, r)
+    outs = gc.keyswitch_batch_dev(level, np.stack([ct[1] for ct in cts]), [evk_dev] * 5, has_c0=False)
+    for r, o in zip(refs, outs):
+        assert np.array_equal(o, r)
     gc.lib.B200_DevFree(evk_dev)
+
+
+# The configurations bench.py times (and its neighbours), at full size, through the device-resident batch entry point:
+#   bench chain            logN=16, L=24 (60 + 23x45 bit), k=3 (61 bit), beta=8: 23 limbs on the FP64 path, 4 on the integer path
+#   integer-path chain     50-55-bit scale primes (ordinary for bootstrappable parameter sets): every limb on the integer path
+#   beta does not divide L logN=16, L=10, k=3: beta=4 with a single-limb last digit
+# (N/1024) * W * n is far above the fused-kernel threshold in all three, so this is ntt2_ip_kernel<ArithF64> and <ArithInt>,
+# ntt_forward_first and the raw-double ModUp hand-off, word for word against oracle.Ctx.keyswitch.
+BENCH_CASES = [
+    (16, [60] + [45] * 23, [61] * 3, 8),
+    (16, [60] + [52, 55, 50, 53] * 3, [61] * 3, 6),
+    (16, [60] + [45] * 9, [61] * 3, 6),
+    (15, [55] + [40] * 12, [61, 61], 12),
+]
+
+
+@pytest.mark.parametrize("case", BENCH_CASES)
+def test_keyswitch_batchdev_at_bench_sizes_equals_the_oracle(orc, b200lib, case):
+    logN, lq, lp, n = case
+    oc, gc = make(orc, b200lib, (logN, lq, lp))
+    rng = np.random.default_rng(12)
+    nmod = oc.nQ + oc.nP
+    level = oc.nQ - 1
+    beta = oc.num_digits(level)
+    evks = [np.stack([oc.uniform_poly(rng, list(range(nmod))) for _ in range(beta * 2)]).reshape(beta, 2, nmod, oc.N) for _ in range(2)]
+    evk_devs = [gc.evk_to_device(e) for e in evks]
+    cts = np.stack([np.stack([oc.uniform_poly(rng, list(range(level + 1))) for _ in range(2)]) for _ in range(n)])
+    which = [z % 2 for z in range(n)]
+    refs = [oc.keyswitch(level, cts[z, 1], evks[which[z]]) for z in range(n)]
+    outs = gc.keyswitch_batch_dev(level, cts[:, 1], [evk_devs[w] for w in which], has_c0=False)
+    for z in range(n):
+        assert np.array_equal(outs[z], refs[z]), "ciphertext %d (no c0)" % z
+    outs = gc.keyswitch_batch_dev(level, cts, [evk_devs[w] for w in which], has_c0=True)
+    for z in range(n):
+        r = refs[z].copy(); r[0] = oc.elementwise("add", refs[z][0], cts[z, 0])
+        assert np.array_equal(outs[z], r), "ciphertext %d (+c0)" % z
+    # a lower level of the same chain (plans are per level; beta changes)
+    lvl = max(1, level - 4)
+    outs = gc.keyswitch_batch_dev(lvl, cts[:, 1, : lvl + 1], [evk_devs[w] for w in which], has_c0=False)
+    for z in range(0, n, 3):
+        assert np.array_equal(outs[z], oc.keyswitch(lvl, cts[z, 1, : lvl + 1], evks[which[z]])), "level %d ciphertext %d" % (lvl, z)
+    for e in evk_devs:
+        gc.lib.B200_DevFree(e)
+
+
+def _rerun(env_extra, k):
+    import os, subprocess, sys
+    env = dict(os.environ, **env_extra)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_primitives.py", "-k", k],
+                       cwd=root, env=env, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_fused_inner_product_switch_gives_the_oracles_words(fused):
+    """ORION_B200_FUSED_IP=1 forces the fused second-pass + inner-product kernel (ntt2_ip_kernel) on every chain of CASES,
+    =0 forces the un-fused pair of launches; by default the library picks by size.  The switch is read per call, but the
+    parity cases run in a child process so the setting cannot leak."""
+    _rerun({"ORION_B200_FUSED_IP": fused}, "keyswitch_stages or rescale or batchdev")
 
 
 def test_cluster_ntt_switch_gives_the_same_words():

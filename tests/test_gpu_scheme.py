@@ -251,8 +251,11 @@ def test_bootstrap(orc, b200lib, num_slots):
     rng = np.random.default_rng(8)
     slots = 2048
     base = rng.uniform(-1, 1, num_slots)
-    x = np.tile(base, slots // num_slots)                 # sparse packing == a periodic full-slot vector
-    pt = B.B200_EncodeF64(x, slots, 1, float(1 << 40))
+    # Orion hands Bootstrap a ZERO-PADDED full-slot vector (orion/nn/operations.py:59-60,85-87) and the Go shim multiplies
+    # Lattigo's result by MaxSlots/numSlots (LG/bootstrapper.go:73-74): x, 0, ..., 0 comes back as x, x, ..., x
+    xin = np.zeros(slots); xin[:num_slots] = base
+    x = np.tile(base, slots // num_slots)
+    pt = B.B200_EncodeF64(xin, slots, 1, float(1 << 40))
     ct = B.Encrypt(pt)
     out = B.Bootstrap(ct, num_slots)
     assert B.GetCiphertextLevel(out) == len(logq) - 1
@@ -261,13 +264,14 @@ def test_bootstrap(orc, b200lib, num_slots):
     re, im = np.empty(slots), np.empty(slots)
     B.B200_DecodeF64(p, re, im)
     err = np.max(np.abs(re - x))
-    assert err < 2e-4, err
-    assert np.max(np.abs(im)) < 2e-4
+    tol = 2e-4 * max(1, (slots // num_slots) // 2)        # the post-factor multiplies the bootstrapping error as well
+    assert err < tol, err
+    assert np.max(np.abs(im)) < tol
     # the refreshed ciphertext is usable: one multiplication + rescale
     sq = B.Rescale(B.MulRelinCiphertextNew(out, out))
     p2 = B.Decrypt(sq)
     B.B200_DecodeF64(p2, re, im)
-    assert np.max(np.abs(re - x * x)) < 5e-4
+    assert np.max(np.abs(re - x * x)) < 2.5 * tol
     B.DeleteBootstrappers()
     B.DeleteScheme()
 
