@@ -41,6 +41,7 @@ uint64_t B200_GaloisElement(void* ctx, int rot);            /* 5^rot mod 2N; lat
 /* ---- stream, timing, memory ---- */
 void     B200_Sync(void);
 unsigned long long B200_LaunchCount(void);                   /* kernels launched by this library so far */
+double   B200_AlgorithmicBytes(void);          /* running sum of SURVEY 8(d) algorithmic bytes of the evaluator ops issued so far */
 void*    B200_Stream(void);                                  /* cudaStream_t all work is issued on */
 void     B200_TimerStart(void);                              /* CUDA events on that stream */
 float    B200_TimerStopMs(void);
@@ -48,8 +49,11 @@ float    B200_TimerStopMs(void);
  * inner product, FP64-path limbs) is bracketed by CUDA events on its own stream; ReadMs returns the summed kernel time
  * and the launch count since the last read.  Measurement aid for bench.py's roofline object. */
 void     B200_HostProfDump(void);                            /* ORION_B200_HOSTPROF=1: print and reset the host-side enqueue timers */
-void     B200_ProbeEnable(int on);
-double   B200_ProbeReadMs(long* launches);
+void     B200_ProbeEnable(int mode);              /* 0 off, 1 the dominant kernel only (slot 0), 2 every key-switch stage */
+double   B200_ProbeReadMs(long* launches);        /* slot 0 */
+int      B200_ProbeSlots(void);
+const char* B200_ProbeSlotName(int slot);
+double   B200_ProbeReadSlotMs(int slot, long* launches);
 void*    B200_DevAlloc(size_t words);
 void     B200_DevFree(void* dev);
 void     B200_Upload(void* dev, const uint64_t* host, size_t words);

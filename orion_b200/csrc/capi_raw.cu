@@ -57,6 +57,7 @@ uint64_t B200_ContextPsi(void* h, int idx) { return R(h)->ctx->psi[idx]; }
 
 void B200_Sync(void) { ensure_device(); OB_CUDA(cudaDeviceSynchronize()); }        // main stream, dataflow lanes and side streams
 unsigned long long B200_LaunchCount(void) { return g_launches; }
+double B200_AlgorithmicBytes(void) { return g_alg_bytes; }
 void* B200_Stream(void) { return (void*)stream(); }
 void B200_TimerStart(void) {
     if (!g_ev0) { OB_CUDA(cudaEventCreate(&g_ev0)); OB_CUDA(cudaEventCreate(&g_ev1)); }
@@ -70,8 +71,11 @@ float B200_TimerStopMs(void) {
     return ms;
 }
 void B200_HostProfDump(void) { hostprof_dump(); }
-void B200_ProbeEnable(int on) { probe_enable(on != 0); }
-double B200_ProbeReadMs(long* launches) { return probe_read_ms(launches); }
+void B200_ProbeEnable(int mode) { probe_enable(mode); }
+double B200_ProbeReadMs(long* launches) { return probe_read_ms(launches, PROBE_IP_F64); }
+int B200_ProbeSlots(void) { return PROBE_SLOTS; }
+const char* B200_ProbeSlotName(int slot) { return probe_slot_name(slot); }
+double B200_ProbeReadSlotMs(int slot, long* launches) { return probe_read_ms(launches, slot); }
 
 void* B200_DevAlloc(size_t words) { ensure_device(); void* p; OB_CUDA(cudaMallocAsync(&p, words * 8, stream())); return p; }
 void B200_DevFree(void* p) { if (p) OB_CUDA(cudaFreeAsync(p, stream())); }

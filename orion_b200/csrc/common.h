@@ -27,6 +27,10 @@ namespace ob {
 
 // launch counter: every kernel of this library goes through OB_LAUNCH so bench.py can report gpu_launches
 extern unsigned long long g_launches;
+// algorithmic-byte counter (compulsory HBM traffic -- operands read once, results written once): every
+// evaluator-level operation adds its figure, so a whole inference's roofline is (sum over the ops it ran) / time / peak
+extern double g_alg_bytes;
+inline void alg_bytes(double b) { g_alg_bytes += b; }
 // Launches can be programmatic dependent launches (PDL): the next kernel of the stream may be scheduled while this one
 // drains, and blocks in OB_PDL_SYNC() -- the first statement of EVERY kernel of this library -- until its predecessor has
 // completed and flushed.  Overlaps the tail wave of large kernels with the head of the next; policy in context.cu
@@ -34,10 +38,17 @@ extern unsigned long long g_launches;
 bool pdl_enabled();
 // Kernel probe: while enabled, the launcher of the key switch's dominant kernel brackets it with CUDA events on its own
 // stream (bench.py's roofline.achieved); probe_read sums the elapsed times and clears the list.
-void probe_enable(bool on);
-void probe_begin();
-void probe_end();
-double probe_read_ms(long* launches);
+// Slots name the stages of a key switch (PROBE_* below); slot 0 is the dominant kernel.  Events between launches keep the
+// next kernel from starting early (no PDL overlap across a probe), so bench.py enables only slot 0 inside the timed region
+// and all slots in a separate pass for the per-stage split.
+enum ProbeSlot { PROBE_IP_F64 = 0, PROBE_IP_INT, PROBE_INTT_C1, PROBE_MODUP, PROBE_NTT1_DIGITS, PROBE_INTT_P, PROBE_MODDOWN_BC,
+                 PROBE_MODDOWN_NTT1, PROBE_MODDOWN_FIN, PROBE_SLOTS };
+const char* probe_slot_name(int slot);
+void probe_enable(int mask_or_on);            // 0 off, 1 slot 0 only, 2 every slot
+void probe_begin(int slot = PROBE_IP_F64);
+void probe_end(int slot = PROBE_IP_F64);
+double probe_read_ms(long* launches, int slot = PROBE_IP_F64);
+struct ProbeScope { int s; explicit ProbeScope(int slot) : s(slot) { probe_begin(s); } ~ProbeScope() { probe_end(s); } };
 // Host-side enqueue profiler (ORION_B200_HOSTPROF=1): scoped wall-clock timers around the host work of the hot path
 // (launch API, allocator, plan lookups, events); B200_HostProfDump prints the table.  Off: one predictable branch.
 struct HostProf { int id; unsigned long long t0; explicit HostProf(int i); ~HostProf(); };

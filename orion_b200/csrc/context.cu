@@ -7,6 +7,7 @@
 namespace ob {
 
 unsigned long long g_launches = 0;
+double g_alg_bytes = 0;
 static cudaStream_t g_stream = nullptr;
 static bool g_dev_ok = false;
 
@@ -65,24 +66,33 @@ bool pdl_enabled() {
     return forced >= 0 ? forced == 1 : g_pdl_auto;
 }
 namespace {
-bool g_probe_on = false;
-std::vector<std::pair<cudaEvent_t, cudaEvent_t>>& probe_events() { static auto* v = new std::vector<std::pair<cudaEvent_t, cudaEvent_t>>(); return *v; }
+int g_probe_mode = 0;
+typedef std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ProbeList;
+ProbeList* probe_events() { static auto* v = new ProbeList[PROBE_SLOTS]; return v; }
+bool probe_active(int slot) { return g_probe_mode == 2 || (g_probe_mode == 1 && slot == PROBE_IP_F64); }
 }
-void probe_enable(bool on) { g_probe_on = on; }
-void probe_begin() {
-    if (!g_probe_on) return;
+const char* probe_slot_name(int slot) {
+    static const char* names[PROBE_SLOTS] = {"fused_ntt2_inner_product_f64", "fused_ntt2_inner_product_int", "intt_c1", "modup_base_conversion",
+                                             "ntt_first_pass_digits", "intt_p", "moddown_base_conversion", "moddown_ntt_first_pass",
+                                             "moddown_ntt2_submul"};
+    return slot >= 0 && slot < PROBE_SLOTS ? names[slot] : "";
+}
+void probe_enable(int mode) { g_probe_mode = mode; }
+void probe_begin(int slot) {
+    if (!probe_active(slot)) return;
     cudaEvent_t a, b;
     OB_CUDA(cudaEventCreate(&a)); OB_CUDA(cudaEventCreate(&b));
     OB_CUDA(cudaEventRecord(a, stream()));
-    probe_events().push_back({a, b});
+    probe_events()[slot].push_back({a, b});
 }
-void probe_end() {
-    if (!g_probe_on) return;
-    OB_CUDA(cudaEventRecord(probe_events().back().second, stream()));
+void probe_end(int slot) {
+    if (!probe_active(slot)) return;
+    OB_CUDA(cudaEventRecord(probe_events()[slot].back().second, stream()));
 }
-double probe_read_ms(long* launches) {
+double probe_read_ms(long* launches, int slot) {
     double tot = 0;
-    auto& ev = probe_events();
+    if (slot < 0 || slot >= PROBE_SLOTS) { if (launches) *launches = 0; return 0; }
+    auto& ev = probe_events()[slot];
     for (auto& e : ev) {
         OB_CUDA(cudaEventSynchronize(e.second));
         float ms = 0; OB_CUDA(cudaEventElapsedTime(&ms, e.first, e.second));

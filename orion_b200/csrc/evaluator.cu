@@ -110,9 +110,10 @@ void PolyEvaluator::moddown_n(int level, const u64* acc, int acc_stride, int n, 
     }
     const ModDownNPlan& mp = it->second;
     DevBuf pc((size_t)n * K * N * 8), conv((size_t)n * L * N * 8);
-    ntt_inverse(ctx, acc, pc.u(), mp.intt);
-    base_convert_batch(ctx, mp.bc, pc.u(), conv.u(), true);
-    ntt_forward_first(ctx, conv.u(), conv.u(), mp.ntt);
+    { ProbeScope ps(PROBE_INTT_P); ntt_inverse(ctx, acc, pc.u(), mp.intt); }
+    { ProbeScope ps(PROBE_MODDOWN_BC); base_convert_batch(ctx, mp.bc, pc.u(), conv.u(), true); }
+    { ProbeScope ps(PROBE_MODDOWN_NTT1); ntt_forward_first(ctx, conv.u(), conv.u(), mp.ntt); }
+    ProbeScope ps(PROBE_MODDOWN_FIN);
     ntt2_submul(ctx, L, n, acc, acc_stride, conv.u(), ctx.d_pinv.as<ulonglong2>(), addend, addend_stride, addend_polys,
                 addend_period, addend_zstride, out, out_stride);
 }
@@ -150,8 +151,9 @@ void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n,
     }
     const DecompNPlan& dp = it->second;
     DevBuf coef((size_t)n * L * ctx.N * 8);
-    ntt_inverse(ctx, c1s, coef.u(), dp.intt);
-    base_convert_batch(ctx, dp.bc, coef.u(), digits, false);
+    { ProbeScope ps(PROBE_INTT_C1); ntt_inverse(ctx, c1s, coef.u(), dp.intt); }
+    { ProbeScope ps(PROBE_MODUP); base_convert_batch(ctx, dp.bc, coef.u(), digits, false); }
+    ProbeScope ps(PROBE_NTT1_DIGITS);
     if (second_pass) ntt_forward(ctx, digits, digits, dp.ntt);
     else ntt_forward_first(ctx, digits, digits, dp.ntt);
 }
@@ -168,6 +170,7 @@ void PolyEvaluator::keyswitch(int level, const u64* c1_ntt, const u64* evk, cons
                               int addend_polys, u64* out, int out_stride) {
     OB_HP("keyswitch (total)");
     const KsPlan& p = ks_plan(level);
+    alg_bytes(8.0 * ctx.N * (4.0 * p.L + 2.0 * p.beta * p.W));                  // ct in + evk + ct out
     DevBuf digits(digits_words(level) * 8), acc((size_t)2 * p.W * ctx.N * 8);
     decompose(level, c1_ntt, digits.u());
     ks_inner_product(ctx, level, c1_ntt, digits.u(), evk, acc.u(), nullptr, false);
@@ -178,6 +181,7 @@ void PolyEvaluator::keyswitch_n(int level, int n, const u64* c1s, int c1_zstride
                                 int addend_zstride, u64* out) {
     const KsPlan& p = ks_plan(level);
     const size_t N = ctx.N, dw = digits_words(level);
+    alg_bytes((double)n * 8.0 * ctx.N * (4.0 * p.L + 2.0 * p.beta * p.W));
     // ciphertexts per launch sequence: enough to fill the GPU in the short kernels, small enough that the digit buffers
     // (beta*W limbs each) stay around 1 GB -- larger working sets measured slower (profiles/: batch 64 at logN=16, L=24)
     const int chunk = (int)std::max<size_t>(4, std::min<size_t>(IPM_MAX, ((size_t)1 << 30) / (dw * 8)));
@@ -201,6 +205,7 @@ void PolyEvaluator::rescale(int level, const u64* in, int in_stride, u64* out, i
     OB_CHECK(level >= 1, "cannot rescale at level 0");
     OB_CHECK(polys >= 1 && polys <= 2, "rescale handles 1 or 2 polynomials");
     const size_t N = ctx.N;
+    alg_bytes(8.0 * N * polys * (2.0 * level + 1.0));                            // (2L + 2(L-1)) N 8 for a ciphertext, L = level+1
     auto& ci = rescale_intt_[polys]; auto& cf = rescale_ntt_[polys];
     int key = level * 4096 + in_stride;
     if (!ci.count(key)) {

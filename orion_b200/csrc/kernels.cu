@@ -138,6 +138,7 @@ mont_kernel(const u64* __restrict__ in, u64* __restrict__ out, int limbs, int L,
 void ew_binary(Context& c, EwOp op, const u64* a, int a_stride, const u64* b, int b_stride, int b_polys,
                u64* out, int out_stride, int polys, int limbs, int L) {
     dim3 grid(c.N / (2 * TPB), limbs, polys);
+    if (op != EW_COPY) alg_bytes(8.0 * c.N * limbs * polys * (op == EW_NEG ? 2.0 : 3.0));       // operands in, result out
 #define OB_EW(OPV) OB_LAUNCH((ew_binary_kernel<OPV>), grid, TPB, 0, stream(), a, a_stride, b, b_stride, \
                              b_polys < 1 ? 1 : b_polys, out, out_stride, limbs, L, c.nQ, c.N, c.dmc())
     switch (op) {
@@ -171,12 +172,14 @@ void ew_mul_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_str
                    const std::vector<u64>& scalars) {
     ScalarTab tab; DevBuf buf; const ulonglong2* s = stage_scalars(c, limbs, L, scalars, tab, buf);
     dim3 grid(c.N / (2 * TPB), limbs, polys);
+    alg_bytes(16.0 * c.N * limbs * polys);
     OB_LAUNCH((ew_scalar_kernel<0>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), tab, s, 0);
 }
 void ew_add_scalar(Context& c, const u64* a, int a_stride, u64* out, int out_stride, int polys, int limbs, int L,
                    const std::vector<u64>& scalars, int only_poly) {
     ScalarTab tab; DevBuf buf; const ulonglong2* s = stage_scalars(c, limbs, L, scalars, tab, buf);
     dim3 grid(c.N / (2 * TPB), limbs, polys);
+    alg_bytes(16.0 * c.N * limbs * (only_poly >= 0 ? 1 : polys));
     OB_LAUNCH((ew_scalar_kernel<1>), grid, TPB, 0, stream(), a, a_stride, out, out_stride, L, c.nQ, c.N, c.dmc(), tab, s, only_poly);
 }
 
@@ -190,17 +193,20 @@ void lin_comb(Context& c, int n, const u64* const* src, const int* stride, const
     }
     if (c0) for (int t = 0; t < L; ++t) a.k[n * LINCOMB_LIMBS + t] = (*c0)[t];
     dim3 grid(c.N / (2 * TPB), L, polys);
+    alg_bytes(8.0 * c.N * L * polys * (n + 1.0));
     OB_LAUNCH(lincomb_kernel, grid, TPB, 0, stream(), a, n, c0 ? 1 : 0, out, L, c.N, c.dmc());
 }
 
 void tensor_product(Context& c, const u64* a, int a_stride, const u64* b, int b_stride, u64* out, int L) {
     dim3 grid(c.N / TPB, L);
+    alg_bytes(8.0 * c.N * L * 7.0);                       // two degree-1 operands in, one degree-2 result out
     OB_LAUNCH(tensor_kernel, grid, TPB, 0, stream(), a, a_stride, b, b_stride, out, L, c.N, c.dmc());
 }
 
 void automorphism_ntt(Context& c, const u64* in, u64* out, int total_limbs, const uint32_t* idx) {
     OB_CHECK(in != out, "automorphism cannot run in place");
     dim3 grid(c.N / TPB, total_limbs);
+    alg_bytes(16.0 * c.N * total_limbs);
     OB_LAUNCH(automorphism_kernel, grid, TPB, 0, stream(), in, out, c.N, idx);
 }
 

@@ -244,6 +244,8 @@ std::unique_ptr<Ciphertext> lt_apply(Scheme& s, const LinearTransform& lt, const
     }
     auto res = s.new_ct(level, 1, in.scale * lt.scale, in.log_slots);
     s.pev->moddown(level, out.u(), 2, nullptr, 0, 0, res->data.u(), L);
+    // ct in, every QP diagonal once, one evaluation key per rotated baby / giant step, ct out
+    alg_bytes(8.0 * N * (4.0 * L + (double)lt.diag_idx.size() * W + (double)((nb - k_first) + (ng - z_first)) * 2.0 * c.num_digits(level) * W));
     return res;
 }
 

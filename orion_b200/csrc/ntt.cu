@@ -658,13 +658,16 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
     }
     const int tiles = c.N >> LOG_E_CONTIG, tpb = 1 << (LOG_E_CONTIG - 3);
     if (nf) {
-        probe_begin();
+        probe_begin(PROBE_IP_F64);
         OB_LAUNCH((ntt2_ip_kernel<ArithF64>), dim3(tiles, nf, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
                   out_zstride, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
-        probe_end();
+        probe_end(PROBE_IP_F64);
     }
-    if (ni) OB_LAUNCH((ntt2_ip_kernel<ArithInt>), dim3(tiles, ni, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
-                      out_zstride, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+    if (ni) {
+        ProbeScope ps(PROBE_IP_INT);
+        OB_LAUNCH((ntt2_ip_kernel<ArithInt>), dim3(tiles, ni, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
+                  out_zstride, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+    }
 }
 
 // out[p][i] = (a[p*a_stride + i] - NTT(b[p*nl + i])) * mulc[i] (+ addend), limbs i < nl of the Q chain, b from ntt_forward_first

@@ -25,12 +25,16 @@ RAW_SIGNATURES = {
     "B200_GaloisElement": ([c_vp, c_int], c_u64),
     "B200_Sync": ([], None),
     "B200_LaunchCount": ([], ctypes.c_ulonglong),
+    "B200_AlgorithmicBytes": ([], ctypes.c_double),
     "B200_Stream": ([], c_vp),
     "B200_TimerStart": ([], None),
     "B200_TimerStopMs": ([], ctypes.c_float),
     "B200_HostProfDump": ([], None),
     "B200_ProbeEnable": ([ctypes.c_int], None),
     "B200_ProbeReadMs": ([ctypes.POINTER(ctypes.c_long)], ctypes.c_double),
+    "B200_ProbeSlots": ([], c_int),
+    "B200_ProbeSlotName": ([c_int], ctypes.c_char_p),
+    "B200_ProbeReadSlotMs": ([c_int, ctypes.POINTER(ctypes.c_long)], ctypes.c_double),
     "B200_DevAlloc": ([c_sz], c_vp),
     "B200_DevFree": ([c_vp], None),
     "B200_Upload": ([c_vp, u64p, c_sz], None),

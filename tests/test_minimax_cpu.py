@@ -34,11 +34,12 @@ def test_composite_sign_meets_the_error_bound(degrees, logalpha, logerr):
     bound = 2.0 ** (-logerr)
     assert np.max(np.abs(hi - 1.0)) <= bound, np.max(np.abs(hi - 1.0))
     assert np.max(np.abs(lo - 0.0)) <= bound, np.max(np.abs(lo))
-    # inside the gap (-alpha, alpha) a composite minimax sign is "don't care" (Lee et al., eprint 2020/834): the last stage
-    # approximates 1 on a narrow interval near 1 and oscillates below it.  The caller multiplies by x (ReLU = x * sign), so
-    # what matters is that the magnitude there stays O(1): |x * p(x)| <= alpha * max|p|.  Recorded bound: 5.
+    # inside the gap (-alpha, alpha) the TRUE minimax composition rises monotonically from 0 to 1.  A float64 exchange
+    # converges to a different polynomial on the narrow last-stage interval (error bound met, but values between -2 and 4
+    # in the gap -- see the module docstring): this assertion is what tells the two apart.
     mid = evaluate_composite(flat, degrees, np.linspace(-2.0 ** -logalpha, 2.0 ** -logalpha, 20001))
-    assert np.max(np.abs(mid)) <= 5.0, np.max(np.abs(mid))
+    assert np.min(mid) >= -bound and np.max(mid) <= 1.0 + bound, (np.min(mid), np.max(mid))
+    assert np.all(np.diff(mid) >= -1e-9)
     assert abs(evaluate_composite(flat, degrees, np.array([0.0]))[0] - 0.5) < 1e-12          # odd composition: p(0) = 1/2
 
 
