@@ -305,7 +305,7 @@ def main():
     # ---- per-stage split: one more step with an event pair around every stage of the key switch (not inside the timed region:
     #      an event between two launches keeps the second from starting early under PDL) ----
     stage_split = None
-    if not args.no_extras:
+    if not args.no_extras or args.ks_only:
         lib.B200_ProbeEnable(2)
         lib.B200_Sync(); lib.B200_TimerStart()
         resident_step(lib, w, 0, passes=1)

@@ -81,6 +81,8 @@ struct NttPlan { const LimbDesc* first = nullptr; const LimbDesc* second = nullp
 NttPlan make_ntt_plan(Context& c, const std::vector<LimbDesc>& limbs);
 void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p);
 void ntt_forward_first(Context& c, const u64* in, u64* out, const NttPlan& p);   // strided pass only (lazy form), see ks_ntt2_inner_product
+void ntt_forward_second(Context& c, u64* buf, const NttPlan& p);                  // contiguous pass only, in place
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p);
+void ntt_inverse_first(Context& c, const u64* in, u64* out, const NttPlan& p);   // contiguous pass only (lazy form), see intt2_bc_prep
 
 }  // namespace ob

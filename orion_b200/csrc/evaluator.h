@@ -53,8 +53,11 @@ class PolyEvaluator {
   private:
     std::map<int, std::unique_ptr<KsPlan>> plans_;
     std::map<int, NttPlan> rescale_intt_[3], rescale_ntt_[3];
-    struct DecompNPlan { NttPlan intt, ntt; BaseConvBatch bc; };
-    struct ModDownNPlan { NttPlan intt, ntt; BaseConvBatch bc; };
+    // fl / n_fl: destination-limb list of the fused conversion + first NTT pass (ntt1_bc); fusable: every conversion has at
+    // most BC_FUSED_MAX_NS source limbs
+    struct DecompNPlan { NttPlan intt, ntt; BaseConvBatch bc; const BcLimbDev* fl = nullptr; int n_fl = 0; bool fusable = false; };
+    struct ModDownNPlan { NttPlan intt, ntt; BaseConvBatch bc; const BcLimbDev* fl = nullptr; int n_fl = 0; bool fusable = false; };
+    const BcLimbDev* upload_bc_limbs(const std::vector<BcLimbDev>& v);
     std::map<std::vector<int>, DecompNPlan> decomp_n_;
     std::map<std::vector<int>, ModDownNPlan> moddown_n_;
 };

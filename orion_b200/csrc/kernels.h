@@ -53,6 +53,13 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
                                   const std::vector<int>& out_base);
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered);
 
+// ---- base conversion fused into the transforms either side of it (ntt.cu: intt2_prep_kernel, ntt1_bc_kernel) ----
+constexpr int BC_FUSED_MAX_NS = 4;
+struct BcLimbDev { uint32_t out_off, mod, conv, d; };       // destination limb: output offset (units of N), chain index, conversion, index in it
+void intt2_bc_prep(Context& c, u64* buf, unsigned char* vout, const BcDev* descs, int n_conv, bool centered);
+void ntt1_bc(Context& c, const u64* ybuf, const unsigned char* vbuf, u64* out, const BcLimbDev* limbs, int n_limbs, const BcDev* descs,
+             bool centered);
+
 // ---- key-switch inner product ----
 // acc[c][t][x] = sum_j digit_j[t][x] * evk[j][c][chain(t)][x]  (evk in Montgomery form, full-chain layout).
 // digit_j limb t is read from `digits + (j*W + t)*N` unless t belongs to digit j itself, in which case it is

@@ -18,6 +18,7 @@
 #include "context.h"
 #include "kernels.h"
 #include <cooperative_groups.h>
+#include <type_traits>
 
 namespace ob {
 
@@ -26,6 +27,7 @@ namespace {
 constexpr int LOG_E_STRIDED = 11;   // 2048 words per tile, 256 threads
 constexpr int LOG_E_CONTIG = 10;    // 1024 words per tile, 128 threads
 constexpr int K2_BITS = 8;          // contiguous pass handles the 8 low index bits
+constexpr int IP_STAGES_DEFAULT = 0;  // key ring of ntt2_ip_kernel<ArithF64> (see there)
 
 __device__ __forceinline__ int insert_bits(int x, int pos, int nb, int v) {
     return ((x >> pos) << (pos + nb)) | (v << pos) | (x & ((1 << pos) - 1));
@@ -239,11 +241,17 @@ __device__ __forceinline__ void inv_radix(const A& ar, typename A::T (&v)[EPT], 
 // distributed shared-memory staging buffer (`stage` = this CTA's 2048-word slice; word g of the limb lives in the slice of
 // the CTA that transforms it next); 2 = the pass's input comes from this CTA's slice.  tile_ / tid_ replace blockIdx.x /
 // threadIdx.x when a CTA walks several tiles or runs two tiles side by side.
-template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL, bool KEEP = false, int IO = 0>
+// LD (first pass of a fused base conversion + NTT, ntt1_bc_kernel): the pass's input values are not loaded but COMPUTED by
+// ld(word index in the limb) -- the converted coefficient, already in the policy's lazy form.
+// RET (last pass of an inverse transform, intt2_prep_kernel): the normalised output words are not stored but returned in
+// retw[] with their word indices in reti[].
+struct NoLd {};
+template <class A, int LOG_E, int NBITS, bool STRIDED, bool FWD, bool FINAL, bool KEEP = false, int IO = 0, class LD = NoLd, bool RET = false>
 __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restrict__ src, u64* __restrict__ dst,
                                          const typename A::TW* __restrict__ tw, const ulonglong2 ni, int logN,
                                          typename A::T* kept = nullptr, const bool raw_in = false,
-                                         u64* stage = nullptr, const int tile_ = -1, const int tid_ = -1) {
+                                         u64* stage = nullptr, const int tile_ = -1, const int tid_ = -1,
+                                         const LD* ld = nullptr, u64* retw = nullptr, int* reti = nullptr) {
     typedef typename A::T T;
     constexpr int LOG_EPT = log_ept(STRIDED, FWD), EPT = 1 << LOG_EPT;
     constexpr int nbits = NBITS;          // compile-time: the round schedule below unrolls into straight-line code
@@ -298,7 +306,12 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
             return gbase[e >> nb] + (STRIDED ? (k << (pos - logC)) * row_stride : (k << pos));
         };
         const bool quad = pos == 0 && nb >= 2;            // a thread owns runs of >= 4 adjacent words: 256-bit accesses
-        if (r == 0) {
+        if (r == 0 && !std::is_same<LD, NoLd>::value) {
+            if constexpr (!std::is_same<LD, NoLd>::value) {
+#pragma unroll
+                for (int e = 0; e < EPT; ++e) v[e] = (*ld)(goff(e));
+            }
+        } else if (r == 0) {
             u64 w[EPT];
             if (IO == 2) {
 #pragma unroll
@@ -343,7 +356,10 @@ __device__ __forceinline__ void ntt_body(const A ar, u64* sm, const u64* __restr
             u64 w[EPT];
 #pragma unroll
             for (int e = 0; e < EPT; ++e) w[e] = !FINAL ? ar.to_raw(v[e]) : (FWD ? ar.final_fwd(v[e]) : ar.final_inv(v[e], ni));
-            if (IO == 1) {
+            if (RET) {
+#pragma unroll
+                for (int e = 0; e < EPT; ++e) { retw[e] = w[e]; reti[e] = goff(e); }
+            } else if (IO == 1) {
                 if (pair_step) {
 #pragma unroll
                     for (int e = 0; e < EPT; ++e)
@@ -400,15 +416,33 @@ ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
 // Own-digit limbs (t inside digit j) come straight from c1.  Two shared-memory tiles alternate so that a digit's first
 // exchange cannot overwrite words a slower warp still reads for the previous digit.
 struct LimbTab { unsigned char t[128]; };
-template <class A>
+// STAGES > 0: the evaluation-key words go through a per-thread shared-memory ring filled with cp.async (LDGSTS.128, L1
+// bypass) STAGES-1 digits ahead of their use.  Every thread copies exactly the 2 x 64 bytes it will multiply itself, so the
+// ring needs no barrier (cp.async.wait_group orders a thread's own copies), and its 64-byte slots are skewed to an 80-byte
+// stride so the four LDS.128 of a quarter-warp fall into distinct bank groups.  The compulsory stream of the kernel (2/3 of
+// its bytes) is then in flight in shared memory instead of being tied to registers right before the multiply.
+constexpr int IP_SLOT_BYTES = 80;
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+__device__ __forceinline__ void lds128(const void* p, u64& a, u64& b) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(p);
+    asm volatile("ld.shared.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "r"(s));
+}
+template <class A, int STAGES>
 __global__ void __launch_bounds__(1 << (LOG_E_CONTIG - 3))
 ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restrict__ digits, size_t dig_zstride,
                const IpMulti m, u64* __restrict__ out, size_t out_zstride, const __grid_constant__ LimbTab tab,
                int L, int K, int nQ, int nmod, int beta, const ModConst* __restrict__ mc,
                const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN) {
     OB_PDL_SYNC();
-    constexpr int EPT = 8, SM_WORDS = (1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3));
-    __shared__ __align__(16) u64 sm[2][SM_WORDS];
+    constexpr int EPT = 8, SM_WORDS = (1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3)), TPB_ = 1 << (LOG_E_CONTIG - 3);
+    extern __shared__ __align__(16) unsigned char ip_smem[];
+    u64 (*sm)[SM_WORDS] = (u64 (*)[SM_WORDS])ip_smem;                        // [2][SM_WORDS] exchange tiles
+    unsigned char* ring = ip_smem + 2 * SM_WORDS * 8;                        // [STAGES][2][TPB_] slots of IP_SLOT_BYTES
     typedef typename A::T T;
     const int t = tab.t[blockIdx.y], z = blockIdx.z, W = L + K;
     const size_t N = (size_t)1 << logN;
@@ -425,14 +459,31 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
 #pragma unroll
     for (int e = 0; e < EPT; ++e) { a0[e] = ar.acc_zero(); a1[e] = ar.acc_zero(); }
     int buf = 0;
-    // L2 prefetch, one 128-byte line per thread: the key tiles of digit j (2 x 8 KB) and the tile of digit j+1 (8 KB), so
-    // that the loads that follow the butterflies find their lines in L2 (the kernel runs at ~20 warps/SM; measured
-    // 3 998 -> 4 275 keyswitch/s; a longer prefetch distance measured the same)
+    // L2 prefetch, one 128-byte line per thread: the key tiles of digit j (2 x 8 KB; direct-load variant only) and the tile
+    // of digit j+1 (8 KB), so that the loads that follow the butterflies find their lines in L2
     const size_t line = ((size_t)blockIdx.x << LOG_E_CONTIG) + (threadIdx.x & 63) * 16;
     const u64* pf_evk = m.evk[z] + ((size_t)(threadIdx.x >> 6) * nmod + ci) * N + line;
     const u64* pf_dig = dz + line;
+    auto stage_keys = [&](int j) {               // copies of digit j's key words into ring slot j % STAGES (empty group past the end)
+        if (STAGES > 0) {
+            if (j < beta) {
+                const u64* k0 = evk + (size_t)j * 2 * nmod * N;
+                const u64* k1 = k0 + (size_t)nmod * N;
+                unsigned char* s0 = ring + ((size_t)((j % STAGES) * 2 + 0) * TPB_ + threadIdx.x) * IP_SLOT_BYTES;
+                unsigned char* s1 = s0 + (size_t)TPB_ * IP_SLOT_BYTES;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { cp_async16(s0 + 16 * c, k0 + 2 * c); cp_async16(s1 + 16 * c, k1 + 2 * c); }
+            }
+            cp_async_commit();
+        }
+    };
+    if (STAGES > 0) {
+#pragma unroll
+        for (int j = 0; j < STAGES - 1; ++j) stage_keys(j);
+    }
     for (int j = 0; j < beta; ++j) {
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_evk + (size_t)j * 2 * nmod * N));
+        if (STAGES > 0) stage_keys(j + STAGES - 1);
+        else asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_evk + (size_t)j * 2 * nmod * N));
         if (threadIdx.x < 64 && j + 1 < beta && j + 1 != own)
             asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_dig + (size_t)(j + 1) * W * N));
         T d[EPT];
@@ -446,15 +497,29 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
                                                                          make_ulonglong2(0, 0), logN, d);
             buf ^= 1;
         }
-        const u64* k0 = evk + (size_t)j * 2 * nmod * N;
-        const u64* k1 = k0 + (size_t)nmod * N;
         u64 k[EPT];
-        ld_global_256(k0, k[0], k[1], k[2], k[3]); ld_global_256(k0 + 4, k[4], k[5], k[6], k[7]);
+        if (STAGES > 0) {
+            cp_async_wait<(STAGES > 0 ? STAGES - 1 : 0)>();
+            const unsigned char* s0 = ring + ((size_t)((j % STAGES) * 2 + 0) * TPB_ + threadIdx.x) * IP_SLOT_BYTES;
+            const unsigned char* s1 = s0 + (size_t)TPB_ * IP_SLOT_BYTES;
 #pragma unroll
-        for (int e = 0; e < EPT; ++e) ar.mac(a0[e], d[e], k[e]);
-        ld_global_256(k1, k[0], k[1], k[2], k[3]); ld_global_256(k1 + 4, k[4], k[5], k[6], k[7]);
+            for (int c = 0; c < 4; ++c) lds128(s0 + 16 * c, k[2 * c], k[2 * c + 1]);
 #pragma unroll
-        for (int e = 0; e < EPT; ++e) ar.mac(a1[e], d[e], k[e]);
+            for (int e = 0; e < EPT; ++e) ar.mac(a0[e], d[e], k[e]);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) lds128(s1 + 16 * c, k[2 * c], k[2 * c + 1]);
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) ar.mac(a1[e], d[e], k[e]);
+        } else {
+            const u64* k0 = evk + (size_t)j * 2 * nmod * N;
+            const u64* k1 = k0 + (size_t)nmod * N;
+            ld_global_256(k0, k[0], k[1], k[2], k[3]); ld_global_256(k0 + 4, k[4], k[5], k[6], k[7]);
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) ar.mac(a0[e], d[e], k[e]);
+            ld_global_256(k1, k[0], k[1], k[2], k[3]); ld_global_256(k1 + 4, k[4], k[5], k[6], k[7]);
+#pragma unroll
+            for (int e = 0; e < EPT; ++e) ar.mac(a1[e], d[e], k[e]);
+        }
     }
     u64* o0 = out + (size_t)z * out_zstride + (size_t)t * N + off;
     u64* o1 = o0 + (size_t)W * N;
@@ -511,6 +576,156 @@ ntt2_submul_kernel(const u64* __restrict__ a, int a_stride, const u64* __restric
         ntt2_submul_body<ArithF64>(ArithF64(m), sm, ap, bp, ad, op, twd_all + (size_t)i * N, mulc[i], m.q, logN);
     else
         ntt2_submul_body<ArithInt>(ArithInt(m), sm, ap, bp, ad, op, tw_all + (size_t)i * N, mulc[i], m.q, logN);
+}
+
+// ---- base conversion fused into the transforms either side of it (key switch: ModUp and ModDown) -------------------------
+// Un-fused, a base conversion is a round trip of its own: INTT (2 passes) -> conversion kernel (reads ns limbs, writes nd
+// limbs) -> first NTT pass (reads and writes nd limbs).  Fused:
+//   intt2_prep_kernel : the LAST pass of the inverse transform, one CTA per (tile, conversion) walking the conversion's ns
+//                       source limbs: it leaves y_i = x_i * (Q_S/q_i)^-1 mod q_i in place of the coefficient x_i (as an exact
+//                       double when every source prime is an FP64-path prime, else as a word) and the overflow count
+//                       v = floor(sum_i y_i / q_i) -- Lattigo's float64 estimate, same operations in the same order as
+//                       baseconv_batch_kernel -- as one byte per coefficient.
+//   ntt1_bc_kernel    : the FIRST pass of the forward transform of every destination limb computes its inputs from y and v
+//                       (ns multiply-accumulates + the -v Q_S correction) instead of loading a converted limb.
+// The converted limbs are then written once (lazy inter-pass form) and never read back before the second pass; the y limbs
+// (ns per conversion, shared by all its destinations) are served from L2.  Same words as the un-fused path: every value
+// is the same exact residue, only the place where it is computed moves.  ns <= BCF_MAX_NS (raw 128-bit accumulation is
+// valid for any four primes below 2^62; more sources fall back to the un-fused path).
+constexpr int BCF_MAX_NS = 4;
+struct BcLimb { uint32_t out_off, mod, conv, d; };      // destination limb: where it is written, its modulus, its conversion and index in it
+
+template <int S1, bool CENTERED>
+__global__ void __launch_bounds__(1 << (LOG_E_STRIDED - log_ept(true, false)))
+intt2_prep_kernel(u64* buf, unsigned char* __restrict__ vout, const BcDev* __restrict__ descs, const ModConst* __restrict__ mc,
+                  const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, const ulonglong2* __restrict__ ninv_all, int logN) {
+    OB_PDL_SYNC();
+    constexpr int EPT = 1 << log_ept(true, false);
+    __shared__ __align__(16) u64 sm[(1 << LOG_E_STRIDED) + (1 << (LOG_E_STRIDED - 3))];
+    const BcDev d = descs[blockIdx.y];
+    const size_t N = (size_t)1 << logN;
+    double vf[EPT];
+    int gi[EPT];
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) vf[e] = 0.0;
+    for (int i = 0; i < d.ns; ++i) {
+        const int ci = d.src_mod[i];
+        const ModConst& m = mc[ci];
+        u64* limb = buf + (size_t)(d.in_off + i) * N;
+        const ulonglong2 ni = ninv_all[ci];
+        u64 w[EPT];
+        if (m.bits <= F64_MAX_BITS)
+            ntt_body<ArithF64, LOG_E_STRIDED, S1, true, false, true, false, 0, NoLd, true>(ArithF64(m), sm, limb, nullptr, twd_all + (size_t)ci * N, ni, logN,
+                                                                                           nullptr, false, nullptr, -1, -1, nullptr, w, gi);
+        else
+            ntt_body<ArithInt, LOG_E_STRIDED, S1, true, false, true, false, 0, NoLd, true>(ArithInt(m), sm, limb, nullptr, tw_all + (size_t)ci * N, ni, logN,
+                                                                                           nullptr, false, nullptr, -1, -1, nullptr, w, gi);
+        const ulonglong2 inv = d.inv[i];
+        const u64 q = m.q, half = CENTERED ? d.half_src[i] : 0;
+        const double qd = m.qd;
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) {
+            u64 x = w[e];
+            if (CENTERED) x = add_mod(x, half, q);
+            const u64 y = shoup_mul(x, inv.x, inv.y, q);
+            const double yd = __ull2double_rn(y);
+            vf[e] = __dadd_rn(vf[e], __ddiv_rn(yd, qd));
+            limb[gi[e]] = d.f64_src ? (u64)__double_as_longlong(yd) : y;
+        }
+        __syncthreads();                                     // the next limb's first exchange reuses sm
+    }
+    unsigned char* vo = vout + (size_t)blockIdx.y * N;
+    const bool single = d.ns == 1 && !CENTERED;              // a single source without centring: v is 0 by definition
+#pragma unroll
+    for (int e = 0; e < EPT; ++e) vo[gi[e]] = single ? 0 : (unsigned char)(int)vf[e];
+}
+
+// input of a destination limb's first NTT pass, computed from the conversion's y limbs and overflow bytes
+template <class A, bool CENTERED>
+struct BcLoader {
+    const u64* y[BCF_MAX_NS];          // source limbs (y form)
+    const unsigned char* v;
+    const double* s_negd;              // shared memory: [ns+1] doubles, [ns+1] words
+    const u64* s_neg;
+    double wd[BCF_MAX_NS];             // (Q_S/q_i) mod p_t, standard form, exact double (FP64 contraction)
+    u64 wm[BCF_MAX_NS];                // the same in Montgomery form (integer contraction)
+    u64 q, qinv_neg, half_dst;
+    int ns;
+    bool f64_src, f64_mac, raw_ok;
+    A ar;
+    __device__ __forceinline__ typename A::T operator()(int gi) const {
+        const int vb = v[gi];
+        if constexpr (std::is_same<A, ArithF64>::value) {
+            if (f64_mac) {                                   // sources and destination on the FP64 path
+                double a = s_negd[vb];
+#pragma unroll
+                for (int i = 0; i < BCF_MAX_NS; ++i)
+                    if (i < ns) a = __dadd_rn(a, ar.mulmod(__longlong_as_double((long long)y[i][gi]), wd[i]));
+                if (!raw_ok) ar.recentre(a);
+                return a;
+            }
+        }
+        u64 hi = 0, lo = 0;
+#pragma unroll
+        for (int i = 0; i < BCF_MAX_NS; ++i)
+            if (i < ns) {
+                const u64 raw = y[i][gi];
+                const u64 yi = f64_src ? (u64)__double2ull_rn(__longlong_as_double((long long)raw)) : raw;
+                const u64 pl = yi * wm[i], ph = __umul64hi(yi, wm[i]);
+                lo += pl; hi += ph + (lo < pl);
+            }
+        u64 r = add_mod(mont_redc(hi, lo, q, qinv_neg), s_neg[vb], q);
+        if (CENTERED) r = sub_mod(r, half_dst, q);
+        return ar.from_word(r);
+    }
+};
+
+template <int S1, bool CENTERED>
+__global__ void __launch_bounds__(1 << (LOG_E_STRIDED - log_ept(true, true)))
+ntt1_bc_kernel(const u64* __restrict__ ybuf, const unsigned char* __restrict__ vbuf, u64* out, const BcLimb* __restrict__ limbs,
+               const BcDev* __restrict__ descs, const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all,
+               const double* __restrict__ twd_all, int logN) {
+    OB_PDL_SYNC();
+    __shared__ __align__(16) u64 sm[(1 << LOG_E_STRIDED) + (1 << (LOG_E_STRIDED - 3))];
+    __shared__ double s_negd[BCF_MAX_NS + 1];
+    __shared__ u64 s_neg[BCF_MAX_NS + 1];
+    const BcLimb bl = limbs[blockIdx.y];
+    const BcDev d = descs[bl.conv];
+    const size_t N = (size_t)1 << logN;
+    const ModConst& m = mc[bl.mod];
+    if (threadIdx.x <= d.ns) {
+        s_negd[threadIdx.x] = d.negvq_d[(size_t)bl.d * (d.ns + 1) + threadIdx.x];
+        s_neg[threadIdx.x] = d.negvq[(size_t)bl.d * (d.ns + 1) + threadIdx.x];
+    }
+    __syncthreads();
+    u64* dst = out + (size_t)bl.out_off * N;
+    const ulonglong2 ni = make_ulonglong2(0, 0);
+    auto fill = [&](auto& ld) {
+#pragma unroll
+        for (int i = 0; i < BCF_MAX_NS; ++i) {
+            const bool on = i < d.ns;
+            ld.y[i] = on ? ybuf + (size_t)(d.in_off + i) * N : nullptr;
+            ld.wd[i] = on ? d.mat_d[(size_t)i * d.nd + bl.d] : 0.0;
+            ld.wm[i] = on ? d.mat[(size_t)i * d.nd + bl.d] : 0;
+        }
+        ld.v = vbuf + (size_t)bl.conv * N;
+        ld.s_negd = s_negd; ld.s_neg = s_neg;
+        ld.q = m.q; ld.qinv_neg = m.qinv_neg; ld.half_dst = CENTERED ? d.half_dst[bl.d] : 0;
+        ld.ns = d.ns; ld.f64_src = d.f64_src != 0;
+        ld.f64_mac = !CENTERED && d.f64_src && m.bits <= F64_MAX_BITS;
+        ld.raw_ok = d.ns <= 4;                               // growth bound of the forward butterflies (kernels.h bc_raw_out)
+    };
+    if (m.bits <= F64_MAX_BITS) {
+        BcLoader<ArithF64, CENTERED> ld{{}, nullptr, nullptr, nullptr, {}, {}, 0, 0, 0, 0, false, false, false, ArithF64(m)};
+        fill(ld);
+        ntt_body<ArithF64, LOG_E_STRIDED, S1, true, true, false, false, 0, BcLoader<ArithF64, CENTERED>>(
+            ArithF64(m), sm, nullptr, dst, twd_all + (size_t)bl.mod * N, ni, logN, nullptr, false, nullptr, -1, -1, &ld);
+    } else {
+        BcLoader<ArithInt, CENTERED> ld{{}, nullptr, nullptr, nullptr, {}, {}, 0, 0, 0, 0, false, false, false, ArithInt(m)};
+        fill(ld);
+        ntt_body<ArithInt, LOG_E_STRIDED, S1, true, true, false, false, 0, BcLoader<ArithInt, CENTERED>>(
+            ArithInt(m), sm, nullptr, dst, tw_all + (size_t)bl.mod * N, ni, logN, nullptr, false, nullptr, -1, -1, &ld);
+    }
 }
 
 // Whole-limb NTT / INTT in ONE launch for small rings (2^12 <= N <= 2^14): a thread-block cluster of N/2048 CTAs owns one
@@ -635,6 +850,14 @@ void ntt_forward(Context& c, const u64* in, u64* out, const NttPlan& p) {
               (const u64*)out, out, p.second, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
 }
 
+// Second (contiguous) pass only, in place on limbs that hold the output of a first pass (ntt_forward_first / ntt1_bc).
+void ntt_forward_second(Context& c, u64* buf, const NttPlan& p) {
+    if (p.n == 0) return;
+    dim3 g2(c.N >> LOG_E_CONTIG, p.n);
+    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, true, true>), g2, 1 << (LOG_E_CONTIG - log_ept(false, true)), 0, stream(),
+              (const u64*)buf, buf, p.second, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN);
+}
+
 // First (strided) pass only: the limbs are left in the policy's lazy inter-pass form for ks_ntt2_inner_product.
 void ntt_forward_first(Context& c, const u64* in, u64* out, const NttPlan& p) {
     if (p.n == 0) return;
@@ -657,17 +880,30 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
         if (c.mc[ci].bits <= F64_MAX_BITS) tf.t[nf++] = (unsigned char)t; else ti.t[ni++] = (unsigned char)t;
     }
     const int tiles = c.N >> LOG_E_CONTIG, tpb = 1 << (LOG_E_CONTIG - 3);
+    constexpr size_t SMX = 2 * ((1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3))) * 8;      // the two exchange tiles
+    // key-ring depth of the FP64 instantiation: ORION_B200_IP_STAGES = 0 (direct loads) / 2 / 3
+    static const int stages = [] { const char* e = std::getenv("ORION_B200_IP_STAGES"); const int v = e ? std::atoi(e) : IP_STAGES_DEFAULT;
+                                   return (v == 2 || v == 3) ? v : 0; }();
+    static bool attr_set = false;
+    if (!attr_set) {
+        OB_CUDA(cudaFuncSetAttribute(ntt2_ip_kernel<ArithF64, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMX + 2 * 2 * tpb * IP_SLOT_BYTES)));
+        OB_CUDA(cudaFuncSetAttribute(ntt2_ip_kernel<ArithF64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMX + 3 * 2 * tpb * IP_SLOT_BYTES)));
+        attr_set = true;
+    }
+#define OB_IP_ARGS c1, c1_zstride, digits, dig_zstride, m, out, out_zstride
     if (nf) {
         probe_begin(PROBE_IP_F64);
-        OB_LAUNCH((ntt2_ip_kernel<ArithF64>), dim3(tiles, nf, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
-                  out_zstride, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        const size_t ring = (size_t)stages * 2 * tpb * IP_SLOT_BYTES;
+        if (stages == 3) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 3>), dim3(tiles, nf, n), tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        else if (stages == 2) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 2>), dim3(tiles, nf, n), tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        else OB_LAUNCH((ntt2_ip_kernel<ArithF64, 0>), dim3(tiles, nf, n), tpb, SMX, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
         probe_end(PROBE_IP_F64);
     }
     if (ni) {
         ProbeScope ps(PROBE_IP_INT);
-        OB_LAUNCH((ntt2_ip_kernel<ArithInt>), dim3(tiles, ni, n), tpb, 0, stream(), c1, c1_zstride, digits, dig_zstride, m, out,
-                  out_zstride, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), dim3(tiles, ni, n), tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
     }
+#undef OB_IP_ARGS
 }
 
 // out[p][i] = (a[p*a_stride + i] - NTT(b[p*nl + i])) * mulc[i] (+ addend), limbs i < nl of the Q chain, b from ntt_forward_first
@@ -678,6 +914,42 @@ void ntt2_submul(Context& c, int nl, int polys, const u64* a, int a_stride, cons
     OB_LAUNCH(ntt2_submul_kernel, dim3(c.N >> LOG_E_CONTIG, nl, polys), 1 << (LOG_E_CONTIG - 3), 0, stream(), a, a_stride, b, nl,
               addend, addend_stride, addend_polys, addend_period, addend_zstride, out, out_stride, mulc, c.dmc(),
               c.tw_fwd(), c.twd_fwd(), c.logN);
+}
+
+// First (contiguous) pass of the inverse transform only: the limbs are left in the policy's lazy inter-pass form for intt2_prep.
+void ntt_inverse_first(Context& c, const u64* in, u64* out, const NttPlan& p) {
+    if (p.n == 0) return;
+    dim3 g2(c.N >> LOG_E_CONTIG, p.n);
+    OB_LAUNCH((ntt_pass<LOG_E_CONTIG, K2_BITS, false, false, false>), g2, 1 << (LOG_E_CONTIG - log_ept(false, true)), 0, stream(),
+              in, out, p.first, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN);
+}
+
+// buf: source limbs after ntt_inverse_first (conversion z's sources at (descs[z].in_off + i) * N); on return y form + vout[z][N]
+void intt2_bc_prep(Context& c, u64* buf, unsigned char* vout, const BcDev* descs, int n_conv, bool centered) {
+    if (n_conv == 0) return;
+    const int s1 = c.logN - K2_BITS;
+    dim3 g1(c.N >> LOG_E_STRIDED, n_conv);
+    const int tpb = 1 << (LOG_E_STRIDED - log_ept(true, false));
+#define OB_PREP(S1V) do { if (centered) OB_LAUNCH((intt2_prep_kernel<S1V, true>), g1, tpb, 0, stream(), buf, vout, descs, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN); \
+                          else OB_LAUNCH((intt2_prep_kernel<S1V, false>), g1, tpb, 0, stream(), buf, vout, descs, c.dmc(), c.tw_inv(), c.twd_inv(), c.d_ninv.as<ulonglong2>(), c.logN); } while (0)
+    switch (s1) { case 4: OB_PREP(4); break; case 5: OB_PREP(5); break; case 6: OB_PREP(6); break; case 7: OB_PREP(7); break;
+                  case 8: OB_PREP(8); break; case 9: OB_PREP(9); break; default: OB_FATAL("unsupported logN"); }
+#undef OB_PREP
+}
+
+// first forward NTT pass of every destination limb with its base conversion computed on the fly (see ntt1_bc_kernel)
+void ntt1_bc(Context& c, const u64* ybuf, const unsigned char* vbuf, u64* out, const BcLimbDev* limbs, int n_limbs, const BcDev* descs,
+             bool centered) {
+    if (n_limbs == 0) return;
+    const int s1 = c.logN - K2_BITS;
+    dim3 g1(c.N >> LOG_E_STRIDED, n_limbs);
+    const int tpb = 1 << (LOG_E_STRIDED - log_ept(true, true));
+    const BcLimb* bl = (const BcLimb*)limbs;
+#define OB_N1(S1V) do { if (centered) OB_LAUNCH((ntt1_bc_kernel<S1V, true>), g1, tpb, 0, stream(), ybuf, vbuf, out, bl, descs, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN); \
+                        else OB_LAUNCH((ntt1_bc_kernel<S1V, false>), g1, tpb, 0, stream(), ybuf, vbuf, out, bl, descs, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN); } while (0)
+    switch (s1) { case 4: OB_N1(4); break; case 5: OB_N1(5); break; case 6: OB_N1(6); break; case 7: OB_N1(7); break;
+                  case 8: OB_N1(8); break; case 9: OB_N1(9); break; default: OB_FATAL("unsupported logN"); }
+#undef OB_N1
 }
 
 void ntt_inverse(Context& c, const u64* in, u64* out, const NttPlan& p) {

@@ -194,6 +194,16 @@ def _rerun(env_extra, k):
 
 
 @pytest.mark.parametrize("fused", ["0", "1"])
+def test_fused_base_conversion_switch_gives_the_oracles_words(fused):
+    """ORION_B200_FUSED_BC=1 forces the base conversions of the batched key switch into the transforms either side of them
+    (csrc/ntt.cu intt2_prep_kernel + ntt1_bc_kernel: ModUp inside INTT-last-pass / NTT-first-pass, ModDown likewise) on every
+    chain of CASES and BENCH_CASES -- FP64 and integer contractions, centred and plain, partial digits; =0 forces the
+    un-fused kernels.  By default the library picks by size."""
+    _rerun({"ORION_B200_FUSED_BC": fused, "ORION_B200_FUSED_IP": "1"}, "keyswitch_stages or batchdev")
+    _rerun({"ORION_B200_FUSED_BC": fused, "ORION_B200_FUSED_IP": "0"}, "keyswitch_stages")
+
+
+@pytest.mark.parametrize("fused", ["0", "1"])
 def test_fused_inner_product_switch_gives_the_oracles_words(fused):
     """ORION_B200_FUSED_IP=1 forces the fused second-pass + inner-product kernel (ntt2_ip_kernel) on every chain of CASES,
     =0 forces the un-fused pair of launches; by default the library picks by size.  The switch is read per call, but the
