@@ -131,6 +131,12 @@ void DeleteBootstrappers(void);
 int    B200_ImportCiphertext(const uint64_t* data, int level, int degree, double scale, int logSlots);
 void   B200_ExportCiphertext(int ct, uint64_t* out);
 void*  B200_CiphertextDevicePtr(int ct);
+/* multi-GPU exchange on device memory: receive buffer for a remote ciphertext, stream-ordered access for NCCL (no host
+ * synchronisation), exact scale as hi + lo doubles.  Replaces the gather of SURVEY.md 8(e) (ncclAllGather of layer outputs). */
+int    B200_NewCiphertext(int level, int degree, double scaleHi, double scaleLo, int logSlots);
+void*  B200_CiphertextAcquire(int ct, int for_write);
+void   B200_GetCiphertextScaleParts(int ct, double* hi, double* lo);
+int    B200_GetCiphertextLogSlots(int ct);
 double B200_GetCiphertextScaleF64(int ct);
 void   B200_SetCiphertextScaleF64(int ct, double scale);
 int    B200_ImportPlaintext(const uint64_t* data, int level, double scale);

@@ -133,6 +133,10 @@ SCHEME_SIGNATURES = {
     "B200_ImportCiphertext": ([u64p, c_int, c_int, c_double, c_int], c_int),
     "B200_ExportCiphertext": ([c_int, u64p], None),
     "B200_CiphertextDevicePtr": ([c_int], c_vp),
+    "B200_NewCiphertext": ([c_int, c_int, c_double, c_double, c_int], c_int),
+    "B200_CiphertextAcquire": ([c_int, c_int], c_vp),
+    "B200_GetCiphertextScaleParts": ([c_int, f64p, f64p], None),
+    "B200_GetCiphertextLogSlots": ([c_int], c_int),
     "B200_GetCiphertextScaleF64": ([c_int], c_double),
     "B200_SetCiphertextScaleF64": ([c_int, c_double], None),
     "B200_ImportPlaintext": ([u64p, c_int, c_double], c_int),

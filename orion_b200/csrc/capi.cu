@@ -327,6 +327,33 @@ void* B200_CiphertextDevicePtr(int ct) {                  // the caller touches 
     if (c.trk.ready || !c.trk.busy.empty()) { OB_CUDA(cudaDeviceSynchronize()); c.trk = Track(); }
     return c.data.p;
 }
+// ---- multi-GPU exchange on device memory (orion_b200/parallel.py): NCCL reads / writes a ciphertext's limbs where they live.
+// B200_NewCiphertext allocates an empty ciphertext with the given metadata (the receive buffer of a remote ciphertext);
+// the scale travels as two doubles (hi + lo) so the 64-bit mantissa of the library's long double survives exactly.
+// B200_CiphertextAcquire orders the library's MAIN stream after the handle's last writer (and, for_write, after its readers
+// on other lanes) with device-side event waits only -- no host synchronisation -- and marks the handle as settled on the
+// main stream: external work enqueued on that stream next (torch.distributed with B200_Stream() as the current stream)
+// is ordered after the producers, and every later library call on the handle is ordered after that work.
+int B200_NewCiphertext(int level, int degree, double scaleHi, double scaleLo, int logSlots) {
+    Scheme& s = S();
+    OB_CHECK(level >= 0 && level <= s.max_level && degree >= 1 && degree <= 2, "B200_NewCiphertext: bad level or degree");
+    auto c = s.new_ct(level, degree, (scale_t)scaleHi + (scale_t)scaleLo, logSlots > 0 ? logSlots : s.log_max_slots);
+    return push_ct(std::move(c));
+}
+void* B200_CiphertextAcquire(int ct, int for_write) {
+    Ciphertext& c = CT(ct);
+    Track& t = c.trk;
+    cudaStream_t m = main_stream();
+    if (t.ready && t.home != m) wait_on(m, t.ready);
+    if (for_write) { for (auto& b : t.busy) wait_on(m, b); t.busy.clear(); }
+    t.ready.reset(); t.home = nullptr;
+    return c.data.p;
+}
+void B200_GetCiphertextScaleParts(int ct, double* hi, double* lo) {
+    const scale_t sc = CT(ct).scale;
+    *hi = (double)sc; *lo = (double)(sc - (scale_t)*hi);
+}
+int B200_GetCiphertextLogSlots(int ct) { return CT(ct).log_slots; }
 double B200_GetCiphertextScaleF64(int ct) { return (double)CT(ct).scale; }
 void B200_SetCiphertextScaleF64(int ct, double s) { CT(ct).scale = (scale_t)s; }
 void B200_ExportPlaintext(int pt, uint64_t* out) {
