@@ -229,8 +229,10 @@ def main():
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
+    meta_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        meta_group = dist.new_group(backend="gloo")          # ciphertext metadata of the sharded inference travels host-to-host
 
     from orion_b200 import raw
     lib = raw.load()
@@ -401,6 +403,8 @@ def main():
     resnet = resnet16 = lola = None
     if not args.no_resnet:
         resnet = run_resnet(lib, rank, world, dist if world > 1 else None, torch, peak)
+        if world > 1 and resnet is not None:
+            resnet["strong_scaling"] = run_resnet_sharded(lib, rank, world, dist, torch, meta_group)
         if os.environ.get("ORION_B200_BENCH_RESNET16", "0") != "0":
             resnet16 = run_resnet16(lib, rank, world, dist if world > 1 else None, torch, peak)
         lola = run_lola(lib, rank, world, dist if world > 1 else None, torch)
@@ -544,6 +548,49 @@ def run_resnet(lib, rank, world, dist, torch, peak=None, reps=3):
                 "data": "examples/run_resnet.py flow on a synthetic CIFAR-shaped image: default-init weights, fit on the input; real payloads "
                         "(diagonals, biases, sign polynomials) recorded from the unmodified reference",
                 "e2e": "includes encode+encrypt (H2D) of the image and decrypt+decode (D2H) of the logits"})
+    return res
+
+
+def run_resnet_sharded(lib, rank, world, dist, torch, meta_group, name="resnet20", reps=3):
+    """ONE image across all ranks (strong scaling): block rows of every linear layer round-robin over the ranks, activations and
+    bootstraps where their ciphertext lives, ciphertexts broadcast over NCCL (device limbs) on first remote use."""
+    from orion_b200.bindings import B200Library
+    from orion_b200.parallel import DeviceExchange, ShardedReplayer
+    from orion_b200.replay import Trace
+    gold = os.path.join(ROOT, "tests", "golden")
+    t = Trace(os.path.join(gold, "trace_%s.json" % name), os.path.join(gold, "trace_%s.npz" % name))
+    B = B200Library()
+    B.B200_SetSeed(42)                                          # the same keys on every rank (ranks exchange ciphertexts)
+    x = DeviceExchange(B, 1 << t.meta["config"]["ckks_params"]["LogN"], rank, world, meta_group=meta_group)
+    r = ShardedReplayer(B, t, x, seed=1234)
+    r.setup(); lib.B200_Sync()
+    out = None
+    for _ in range(2):
+        out = r.infer(); lib.B200_Sync()
+    times = []
+    b0, n0, ops0 = x.bytes_moved, x.transfers, r.ops_run
+    for _ in range(reps):
+        lib.B200_Sync(); torch.cuda.synchronize(); dist.barrier(); lib.B200_Sync()
+        lib.B200_TimerStart()
+        out = r.infer()
+        ms = lib.B200_TimerStopMs()
+        torch.cuda.synchronize()
+        tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)               # the image is done when the slowest rank is
+        times.append(float(tt.item()) / 1e3)
+    ops = torch.tensor([float(r.ops_run - ops0) / reps], device="cuda", dtype=torch.float64)
+    allops = [torch.zeros_like(ops) for _ in range(world)]
+    dist.all_gather(allops, ops)
+    res = {"s_per_image": min(times), "n_gpus": world, "scaling": "strong",
+           "ciphertext_broadcasts_per_image": (x.transfers - n0) // reps, "broadcast_bytes_per_image": (x.bytes_moved - b0) // reps,
+           "evaluator_calls_per_rank": [int(o.item()) for o in allops],
+           "note": "limited by the layers whose tensors are a single ciphertext (64-channel stage: 1 ciphertext of 4096 slots at logN=13) -- "
+                   "only one rank works there -- not by NVLink: a broadcast moves 2-4 MB"}
+    if rank == 0 and out is not None:
+        clear = np.array(t.meta["clear_output"], dtype=np.float64)
+        fhe = np.asarray(out, dtype=np.float64)[: clear.size]
+        res["max_abs_err_vs_cleartext"] = float(np.max(np.abs(fhe - clear)))
+    B.DeleteScheme()
     return res
 
 
