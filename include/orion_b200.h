@@ -73,6 +73,7 @@ void B200_BaseConv(void* ctx, const int* src, int ns, const int* dst, int nd, co
 
 /* ---- NTT-domain automorphism X -> X^galEl on n limbs (lattigo/evaluator.go:61-81) ---- */
 void B200_AutomorphismNTT(void* ctx, uint64_t galEl, const uint64_t* in, uint64_t* out, int n);
+void     B200_AutomorphismNTTDev(void* ctx, uint64_t galEl, const void* in_dev, void* out_dev, int n);   /* device buffers, no copies (primitive sweep) */
 
 /* ---- hybrid key switching (lattigo/evaluator.go:61-81, :297-317; HEonGPU operator.cu:1308-1429).
  *      evk host layout: [beta(max level)][2][nQ+nP][N], NTT domain, standard residues. ---- */

@@ -131,6 +131,10 @@ void B200_AutomorphismNTT(void* h, uint64_t galEl, const uint64_t* in, uint64_t*
     automorphism_ntt(*r->ctx, a.u(), b.u(), n, r->ctx->galois_index(galEl));
     d2h(out, b.p, bytes);
 }
+void B200_AutomorphismNTTDev(void* h, uint64_t galEl, const void* in, void* out, int n) {
+    RawCtx* r = R(h);
+    automorphism_ntt(*r->ctx, (const u64*)in, (u64*)out, n, r->ctx->galois_index(galEl));
+}
 uint64_t B200_GaloisElement(void* h, int rot) { return R(h)->ctx->galois_element(rot); }
 
 // ---- evaluation keys: host standard form [beta_max][2][nQ+nP][N] -> device Montgomery form ----

@@ -68,6 +68,14 @@ const KsPlan& PolyEvaluator::ks_plan(int level) {
     return *plans_.emplace(level, std::move(p)).first->second;
 }
 
+// The fused second-pass + inner-product kernel serialises the beta digits of a limb tile inside one CTA, so it needs
+// enough tiles to fill the GPU on its own: large rings / batches only.  ORION_B200_FUSED_IP=0/1 overrides.
+static bool use_fused_ip(const Context& c, int W, int n) {
+    const char* e = std::getenv("ORION_B200_FUSED_IP");
+    if (e && *e) return std::atoi(e) != 0;
+    return (long)(c.N >> 10) * W * n >= 148L * 8;
+}
+
 const BcLimbDev* PolyEvaluator::upload_bc_limbs(const std::vector<BcLimbDev>& v) {
     auto buf = std::make_unique<DevBuf>(v.size() * sizeof(BcLimbDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, v.data(), v.size() * sizeof(BcLimbDev), cudaMemcpyHostToDevice, stream()));
@@ -210,20 +218,22 @@ void PolyEvaluator::decompose_n(int level, const u64* c1s, int c1_stride, int n,
     else ntt_forward_first(ctx, digits, digits, dp.ntt);
 }
 
-// The fused second-pass + inner-product kernel serialises the beta digits of a limb tile inside one CTA, so it needs
-// enough tiles to fill the GPU on its own: large rings / batches only.  ORION_B200_FUSED_IP=0/1 overrides.
-static bool use_fused_ip(const Context& c, int W, int n) {
-    const char* e = std::getenv("ORION_B200_FUSED_IP");
-    if (e && *e) return std::atoi(e) != 0;
-    return (long)(c.N >> 10) * W * n >= 148L * 8;
-}
-
 void PolyEvaluator::keyswitch(int level, const u64* c1_ntt, const u64* evk, const u64* addend, int addend_stride,
                               int addend_polys, u64* out, int out_stride) {
     OB_HP("keyswitch (total)");
     const KsPlan& p = ks_plan(level);
     alg_bytes(8.0 * ctx.N * (4.0 * p.L + 2.0 * p.beta * p.W));                  // ct in + evk + ct out
     DevBuf digits(digits_words(level) * 8), acc((size_t)2 * p.W * ctx.N * 8);
+    if (use_fused_ip(ctx, p.W, 1)) {
+        // large ring: one ciphertext already fills the GPU with one CTA per limb tile -> the fused second pass + inner
+        // product and the fused ModDown epilogue (the path of keyswitch_n; logN=16, L=24: 315 -> 215 us per rotation)
+        decompose_n(level, c1_ntt, p.L, 1, digits.u(), false);
+        IpMulti im{};
+        im.evk[0] = evk; im.scatter[0] = nullptr;
+        ks_ntt2_inner_product(ctx, level, 1, c1_ntt, 0, digits.u(), digits_words(level), im, acc.u(), (size_t)2 * p.W * ctx.N);
+        moddown_n(level, acc.u(), p.W, 2, addend, addend_stride, addend_polys, out, out_stride, 2, 0);
+        return;
+    }
     decompose(level, c1_ntt, digits.u());
     ks_inner_product(ctx, level, c1_ntt, digits.u(), evk, acc.u(), nullptr, false);
     moddown(level, acc.u(), 2, addend, addend_stride, addend_polys, out, out_stride);

@@ -46,6 +46,7 @@ RAW_SIGNATURES = {
     "B200_NTTDev": ([c_vp, c_vp, c_vp, intp, c_int, c_int], None),
     "B200_BaseConv": ([c_vp, intp, c_int, intp, c_int, u64p, u64p, c_int], None),
     "B200_AutomorphismNTT": ([c_vp, c_u64, u64p, u64p, c_int], None),
+    "B200_AutomorphismNTTDev": ([c_vp, c_u64, c_vp, c_vp, c_int], None),
     "B200_EvkToDevice": ([c_vp, u64p], c_vp),
     "B200_KeySwitch": ([c_vp, c_int, u64p, c_vp, u64p, u64p], None),
     "B200_KeySwitchDev": ([c_vp, c_int, c_vp, c_vp, c_vp, c_vp], None),

@@ -276,6 +276,42 @@ def test_bootstrap(orc, b200lib, num_slots):
     B.DeleteScheme()
 
 
+@pytest.mark.parametrize("num_slots,min_bits", [(4096, 18.0), (1024, 16.0)])
+def test_bootstrap_precision_at_the_resnet20_parameter_set(orc, b200lib, num_slots, min_bits):
+    """The shipped ResNet-20 parameters (configs/resnet.yml: logN=13, LogQ 60+32x30, LogP 60x2, LogScale 30, H=192, boot
+    LogP 8x61): a ciphertext at level 1 comes back at level 32 with the default scale and >= 18 bits of precision on full
+    slots (max |error| <= 2^-18 for values in [-1, 1]); with 1024 of 4096 slots the Go shim's post-factor MaxSlots/slots = 4
+    (LG/bootstrapper.go:73-74) multiplies the error as well: >= 16 bits.  Input as Orion sends it: zero-padded."""
+    from orion_b200.bindings import B200Library
+    B = B200Library()
+    B.B200_SetSeed(11)
+    logq = [60] + [30] * 32
+    B.NewScheme(13, logq, [60, 60], 30, 192, "standard", "", "none")
+    try:
+        B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey()
+        B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor(); B.NewEvaluator()
+        B.NewBootstrapper([61] * 8, num_slots)
+        slots = 4096
+        rng = np.random.default_rng(8)
+        base = rng.uniform(-1, 1, num_slots)
+        xin = np.zeros(slots); xin[:num_slots] = base
+        want = np.tile(base, slots // num_slots)
+        ct = B.Encrypt(B.B200_EncodeF64(xin, slots, 1, float(1 << 30)))
+        worst = 0.0
+        for _ in range(2):
+            out = B.Bootstrap(ct, num_slots)
+            assert B.GetCiphertextLevel(out) == 32 and B.GetCiphertextScale(out) == 1 << 30
+            re, im = np.empty(slots), np.empty(slots)
+            B.B200_DecodeF64(B.Decrypt(out), re, im)
+            worst = max(worst, float(np.max(np.abs(re - want))), float(np.max(np.abs(im))))
+        bits = -np.log2(worst)
+        print("bootstrap at the ResNet-20 chain, %d slots: %.1f bits" % (num_slots, bits))
+        assert bits >= min_bits, (bits, worst)
+    finally:
+        B.DeleteBootstrappers()
+        B.DeleteScheme()
+
+
 def test_polynomial_evaluation_words_equal_the_oracles(orc, b200lib):
     """a13, word for word: EvaluatePolynomial (Chebyshev and monomial, degrees 5-31: power basis, Paterson-Stockmeyer
     recursion with backward scale propagation, relinearisations, rescales) gives the ciphertext oracle/scheme.py

@@ -43,6 +43,28 @@ def row(name, logN, L, batch, us, nbytes):
           (name, logN, L, batch, us, 1e6 / us, gbs, gbs / PEAK), flush=True)
 
 
+def cpu_row(logN, Q, P, L, K):
+    """The CPU oracle (OpenMP, all host cores) on the same key switch: a bounded sample, reported beside the GPU rows."""
+    import oracle
+    oc = oracle.Ctx(logN, list(Q) + list(P), len(Q), len(P))
+    oc.L.orc_set_threads(os.cpu_count() or 1)
+    rng = np.random.default_rng(1234)
+    nmod, level = L + K, L - 1
+    beta = oc.num_digits(level)
+    evk = rng.integers(0, 1 << 44, size=(beta, 2, nmod, oc.N), dtype=np.uint64)
+    c1 = oc.uniform_poly(rng, list(range(L)))
+    oc.keyswitch(level, c1, evk)
+    n, t0 = 0, time.perf_counter()
+    while n < 16 and time.perf_counter() - t0 < 2.0:
+        oc.keyswitch(level, c1, evk); n += 1
+    us = (time.perf_counter() - t0) / n * 1e6
+    print("%-26s logN=%2d L=%2d batch=  1  %9.1f us/op  %9.1f op/s  (CPU oracle, %d threads, %d key switches timed)" %
+          ("key switch, CPU oracle", logN, L, us, 1e6 / us, os.cpu_count() or 1, n), flush=True)
+
+
+cpu_rows = False
+
+
 def primitives(logN, L, K=3):
     Q, P = raw.gen_moduli([60] + [45] * (L - 1), [61] * K, logN + 1)
     ctx = raw.RawContext(logN, Q, P)
@@ -69,12 +91,17 @@ def primitives(logN, L, K=3):
     row("INTT (ciphertext)", logN, L, 1, us, 16 * N * 2 * L)
     us = timeit(lambda: lib.B200_RescaleDev(ctx.h, level, bufs[nxt()], outs[st["i"]], 2), reps)
     row("rescale", logN, L, 1, us, 8 * N * (2 * L + 2 * (L - 1)))
+    gal = ctx.galois_element(1)
+    us = timeit(lambda: lib.B200_AutomorphismNTTDev(ctx.h, gal, bufs[nxt()], outs[st["i"]], 2 * L), reps)
+    row("automorphism (NTT domain)", logN, L, 1, us, 2 * 2 * L * N * 8)
     evk = ctx.evk_to_device(rng.integers(0, 1 << 44, size=beta * 2 * nmod * N, dtype=np.uint64))
     ks_bytes = 8 * N * (4 * L + 2 * beta * (L + K))
     us = timeit(lambda: lib.B200_KeySwitchDev(ctx.h, level, bufs[nxt()] + LN * 8, evk, bufs[st["i"]], outs[st["i"]]), reps)
     row("key switch (= rotation)", logN, L, 1, us, ks_bytes)
-    for batch in (8, 64):
-        if batch * (beta * nmod + 6 * L) * N * 8 > (40 << 30):
+    if cpu_rows:
+        cpu_row(logN, Q, P, L, K)
+    for batch in (8, 64, 256):
+        if batch * 4 * LN * 8 > (60 << 30):
             continue
         big_in = lib.B200_DevAlloc(batch * 2 * LN); big_out = lib.B200_DevAlloc(batch * 2 * LN)
         for b in range(batch):
@@ -147,7 +174,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--no-scheme", action="store_true")
+    ap.add_argument("--cpu", action="store_true", help="time the CPU oracle's key switch beside every (logN, L) row group")
     a = ap.parse_args()
+    global cpu_rows
+    cpu_rows = a.cpu
     print("# primitive sweep on %s; measured HBM peak %.0f GB/s; times are CUDA-event averages" % (time.strftime("%Y-%m-%d"), PEAK))
     logNs = (13, 16) if a.quick else (13, 14, 15, 16)
     Ls = (24,) if a.quick else (6, 12, 24)
@@ -156,7 +186,7 @@ def main():
             primitives(logN, L)
     if not a.no_scheme:
         for logN in ((13,) if a.quick else (13, 14, 15, 16)):
-            scheme_level(logN, 12, boot=(logN <= 15))
+            scheme_level(logN, 12, boot=True)
 
 
 if __name__ == "__main__":
