@@ -104,7 +104,7 @@ def lib():
         "orc_special_ifft": ([f64p, f64p, c_int, c_int], None),
         "orc_special_fft": ([f64p, f64p, c_int, c_int], None),
         "orc_encode_round": ([c_vp, f64p, f64p, c_int, ctypes.c_double, intp, c_int, u64p], None),
-        "orc_scaled_const_rns": ([c_vp, ctypes.c_double, ctypes.c_longdouble, intp, c_int, u64p], None),
+        "orc_scaled_const_rns": ([c_vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, intp, c_int, u64p], None),
         "orc_decode_crt": ([c_vp, u64p, c_int, ctypes.c_double, c_int, f64p, f64p], None),
     }
     for name, (args, res) in sig.items():

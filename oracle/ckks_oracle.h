@@ -110,7 +110,7 @@ void orc_special_ifft(double *re, double *im, int log_slots, int M);
 void orc_special_fft(double *re, double *im, int log_slots, int M);
 void orc_encode_round(const orc_ctx *c, const double *re, const double *im, int log_slots, double scale,
                       const int *mods, int nmods, u64 *out);
-void orc_scaled_const_rns(const orc_ctx *c, double v, long double cscale, const int *mods, int n, u64 *out);
+void orc_scaled_const_rns(const orc_ctx *c, double v, double cscale_hi, double cscale_lo, const int *mods, int n, u64 *out);
 void orc_decode_crt(const orc_ctx *c, const u64 *coeffs, int level, double scale, int log_slots, double *re, double *im);
 
 #ifdef __cplusplus

@@ -155,7 +155,10 @@ void orc_decode_crt(const orc_ctx *c, const u64 *coeffs, int level, double scale
 }
 
 /* residues of sign(c) * roundl(|c * cscale|) for the listed moduli (scalar add / mul: LG/evaluator.go:102-179) */
-void orc_scaled_const_rns(const orc_ctx *c, double v, long double cscale, const int *mods, int n, u64 *out) {
+void orc_scaled_const_rns(const orc_ctx *c, double v, double cscale_hi, double cscale_lo, const int *mods, int n, u64 *out) {
+    /* the scale is a long double (64-bit mantissa) on both sides of the parity tests; it crosses the ctypes boundary as
+     * hi + lo doubles because ctypes.c_longdouble silently narrows to a double */
+    long double cscale = (long double)cscale_hi + (long double)cscale_lo;
     long double mag = roundl(fabsl((long double)v * cscale));
     for (int t = 0; t < n; t++) {
         u64 q = orc_ctx_modulus(c, mods[t]);

@@ -32,11 +32,13 @@ class OPt:
 
 
 class OScheme:
-    def __init__(self, logN, logQ, logP, log_scale, h, seed):
+    def __init__(self, logN, logQ, logP, log_scale, h, seed, moduli=None):
+        """moduli = (Q, P): explicit prime chains instead of bit sizes (the bootstrapping scheme extends the residual chain)."""
         from . import gen_moduli
         self.L = lib()
         self.logN, self.N = logN, 1 << logN
-        self.Q, self.Pm = gen_moduli(logQ, logP, logN + 1)
+        self.Q, self.Pm = moduli if moduli is not None else gen_moduli(logQ, logP, logN + 1)
+        self.Q, self.Pm = [int(q) for q in self.Q], [int(q) for q in self.Pm]
         self.nQ, self.nP, self.nmod = len(self.Q), len(self.Pm), len(self.Q) + len(self.Pm)
         self.ctx = Ctx(logN, self.Q + self.Pm, self.nQ, self.nP)
         self.mod = self.Q + self.Pm
@@ -110,7 +112,9 @@ class OScheme:
 
     def _const_rns(self, value, cscale, mods):
         out = np.empty(len(mods), dtype=np.uint64)
-        self.L.orc_scaled_const_rns(self.ctx.h, float(value), ctypes.c_longdouble(cscale), ints(mods), len(mods), P(out))
+        cs = LD(cscale)
+        hi = float(cs)
+        self.L.orc_scaled_const_rns(self.ctx.h, float(value), hi, float(cs - LD(hi)), ints(mods), len(mods), P(out))
         return out
 
     def _pmodq(self, level):
@@ -433,10 +437,12 @@ class OScheme:
         v0 = np.round(abs(LD(c0) * S))
         return self.lin_comb_int(ops, ks, -v0 if c0 < 0 else v0, level, S)
 
-    def poly_evaluate(self, ct, coeffs, chebyshev, out_scale):
+    def poly_evaluate(self, ct, coeffs, chebyshev, out_scale, float32_coeffs=True):
+        """float32_coeffs: the boundary hands coefficients over as C floats (GenerateChebyshev / GenerateMonomial); the
+        bootstrapping circuit's own interpolant (oracle/bootstrap.py) keeps its doubles."""
         def bitlen(x):
             return int(x).bit_length()
-        p = [float(np.float32(c)) for c in coeffs]
+        p = [float(np.float32(c)) if float32_coeffs else float(c) for c in coeffs]
         d = len(p) - 1
         while d > 0 and p[d] == 0.0:
             d -= 1

@@ -143,6 +143,32 @@ struct Bootstrapper {
 };
 std::map<int, std::unique_ptr<Bootstrapper>>& g_boot = *new std::map<int, std::unique_ptr<Bootstrapper>>();     // keyed by slot count (LG/bootstrapper.go:16)
 
+// ORION_B200_BOOT_DUMP=<dir>: every stage of a bootstrap writes its ciphertext words (and the host-side tables) there, for
+// the stage-by-stage comparison with oracle/bootstrap.py (tools/boot_lockstep.py)
+const char* dump_dir() { static const char* d = std::getenv("ORION_B200_BOOT_DUMP"); return d; }
+void dump_raw(const std::string& tag, const void* p, size_t bytes) {
+    const std::string path = std::string(dump_dir()) + "/" + tag + ".bin";
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) return;
+    std::fwrite(p, 1, bytes, f); std::fclose(f);
+}
+void dump_ct(const std::string& tag, const Ciphertext& c, int N) {
+    if (!dump_dir()) return;
+    const size_t bytes = (size_t)(c.degree + 1) * (c.level + 1) * N * 8;
+    std::vector<unsigned char> h(bytes);
+    OB_CUDA(cudaMemcpyAsync(h.data(), c.data.p, bytes, cudaMemcpyDeviceToHost, stream()));
+    OB_CUDA(cudaStreamSynchronize(stream()));
+    dump_raw(tag, h.data(), bytes);
+    const long double sc = c.scale; const double meta[4] = {(double)c.level, (double)c.degree, (double)sc, (double)(sc - (long double)(double)sc)};
+    dump_raw(tag + ".meta", meta, sizeof(meta));
+}
+void dump_diag(const std::string& tag, const DiagMat& m) {
+    if (!dump_dir()) return;
+    std::vector<double> flat;
+    for (auto& kv : m) { flat.push_back((double)kv.first); for (auto& v : kv.second) { flat.push_back(v.real()); flat.push_back(v.imag()); } }
+    dump_raw(tag, flat.data(), flat.size() * 8);
+}
+
 std::vector<double> cheb_interp(int deg, double K1, int r) {
     const int n = deg + 1;
     std::vector<double> f(n), c(n);
@@ -201,6 +227,13 @@ void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
     b->stc_m = dft_factors(log_slots, 2 * s.N, STC_DEPTH, false, roots);
     b->cheb.chebyshev = true;
     b->cheb.coeffs = cheb_interp((1 << CHEB_DEPTH) - 1, (double)b->K1, b->r);
+    if (dump_dir()) {
+        std::vector<u64> chain = Q; chain.insert(chain.end(), P.begin(), P.end());
+        dump_raw("chain", chain.data(), chain.size() * 8);
+        dump_raw("cheb", b->cheb.coeffs.data(), b->cheb.coeffs.size() * 8);
+        for (size_t k = 0; k < b->cts_m.size(); ++k) dump_diag("cts_m" + std::to_string(k), b->cts_m[k]);
+        for (size_t k = 0; k < b->stc_m.size(); ++k) dump_diag("stc_m" + std::to_string(k), b->stc_m[k]);
+    }
     // X^(N/2): i in every slot
     std::vector<double2> iv(1 << bs.log_max_slots, make_double2(0.0, 1.0));
     b->times_i = bs.encode_complex(iv.data(), (int)iv.size(), b->top_level, 1, bs.log_max_slots);
@@ -252,6 +285,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
                 all.push_back(LimbDesc{(uint32_t)(p * (top + 1) + i), (uint32_t)(p * (top + 1) + i), (uint32_t)i, 0});
         ntt_forward(c, ct->data.u(), ct->data.u(), make_ntt_plan(c, all));
     }
+    dump_ct("00_low", *low, N); dump_ct("01_raised", *ct, N);
     // ---- SubSum (sparse packing): project onto the slot subring; multiplies the kept coefficients by g ----
     double g = 1.0;
     for (int i = n_log; i < bs.log_max_slots; ++i) {
@@ -321,11 +355,13 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
         OB_CUDA(cudaStreamSynchronize(stream()));             // encoded on this lane, read by every later bootstrap on any lane
     }
 
+    dump_ct("02_subsum", *ct, N);
     // ---- CoeffsToSlots ----
     for (int k = 0; k < cts_groups; ++k) {
         auto t = lt_apply(bs, *b.cts[k], *ct);
         bs.rescale(*t, *t);
         ct = std::move(t);
+        dump_ct("03_cts" + std::to_string(k), *ct, N);
     }
     if (ct->level > lvl_after_cts) bs.drop_level(*ct, lvl_after_cts);
     ct->scale = s_mod;
@@ -335,6 +371,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
     bs.add_ct(*ct, cj, im, true);                                            // 2i Im(y)
     bs.mul_pt(im, *b.times_i, im);                                           // * i  ->  -2 Im(y)
     bs.mul_int(im, -1, im);                                                  //      ->  u_im / K'
+    dump_ct("04_re", re, N); dump_ct("05_im", im, N);
 
     // ---- EvalMod on both halves ----
     // ORION_B200_BOOT_DEBUG=1: decrypt the EvalMod intermediates (the bootstrapping scheme holds the secret key) and print
@@ -358,6 +395,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
         };
         auto y = poly_evaluate(bs, x, b.cheb, s_cheb);
         report("chebyshev", 0, *y);
+        if (dump_dir()) dump_ct(std::string("06_cheb_") + (&x == &re ? "re" : "im"), *y, N);
         for (int k = 0; k < b.r; ++k) {
             Ciphertext sq;
             bs.mul_relin(*y, *y, sq);
@@ -376,12 +414,14 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
     }
     bs.mul_pt(*vim, *b.times_i, *vim);
     bs.add_ct(*vre, *vim, *ct, false);                                       // sin(2 pi u_re) + i sin(2 pi u_im)
+    dump_ct("07_vre", *vre, N); dump_ct("08_evalmod", *ct, N);
 
     // ---- SlotsToCoeffs ----
     for (int k = 0; k < stc_groups; ++k) {
         auto t = lt_apply(bs, *b.stc[k], *ct);
         bs.rescale(*t, *t);
         ct = std::move(t);
+        dump_ct("09_stc" + std::to_string(k), *ct, N);
     }
     const int out_level = s.max_level;
     if (ct->level > out_level) bs.drop_level(*ct, out_level);

@@ -312,6 +312,48 @@ def test_bootstrap_precision_at_the_resnet20_parameter_set(orc, b200lib, num_slo
         B.DeleteScheme()
 
 
+@pytest.mark.parametrize("num_slots", [2048, 256])
+def test_bootstrap_words_equal_the_oracles(orc, b200lib, num_slots):
+    """a16, word for word: Bootstrap() on the GPU (ScaleUp, ModRaise, SubSum, 4 CoeffsToSlots transforms, EvalMod on both
+    halves -- degree-63 Chebyshev + double-angle steps --, 3 SlotsToCoeffs transforms; ~30 rotations keys, ~100 key switches)
+    returns the ciphertext oracle/bootstrap.py computes on the CPU from the same input ciphertext and seed.  Full and sparse
+    slot counts (the sparse one adds the SubSum rotations and the shim's post-factor)."""
+    from oracle.bootstrap import OBootstrapper
+    from oracle.scheme import OScheme
+    from orion_b200.bindings import B200Library
+    logn, logq, logp, logscale, h, seed = 12, [55, 40, 40, 40, 40], [56, 56], 40, 64, 11
+    B = B200Library()
+    B.B200_SetSeed(seed)
+    B.NewScheme(logn, logq, logp, logscale, h, "standard", "", "none")
+    try:
+        B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey()
+        B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor(); B.NewEvaluator()
+        O = OScheme(logn, logq, logp, logscale, h, seed)
+        O.gen_secret_key(); O.gen_public_key(); O.gen_relin_key()
+        # NewEvaluator generates the power-of-two rotation keys (LG/evaluator.go:25-31): same sampling events on both sides
+        i = 1
+        while i < (1 << O.log_max_slots):
+            O.galois_key(O.ctx.galois_element(i)); i *= 2
+        rng = np.random.default_rng(8)
+        slots = 1 << (logn - 1)
+        xin = np.zeros(slots); xin[:num_slots] = rng.uniform(-1, 1, num_slots)
+        ct = B.Encrypt(B.B200_EncodeF64(xin, slots, 1, float(1 << logscale)))
+        oct_ = O.encrypt(O.encode(xin, 1, 2.0 ** logscale))
+        assert np.array_equal(export_ct(B, O, ct), oct_.data)
+        B.NewBootstrapper([61, 61, 61, 61], num_slots)
+        ob = OBootstrapper(O, [61, 61, 61, 61], num_slots)
+        got = export_ct(B, O, B.Bootstrap(ct, num_slots))
+        want = ob.bootstrap(oct_)
+        assert got.shape == want.data.shape
+        assert np.array_equal(got, want.data), "bootstrapped ciphertext differs from the oracle's"
+        # and it is a bootstrap: the oracle's ciphertext decrypts to replicate(x)
+        dec = np.real(O.decode(O.decrypt(want)))
+        assert np.max(np.abs(dec - np.tile(xin[:num_slots], slots // num_slots))) < 2e-4 * (slots // num_slots)
+    finally:
+        B.DeleteBootstrappers()
+        B.DeleteScheme()
+
+
 def test_polynomial_evaluation_words_equal_the_oracles(orc, b200lib):
     """a13, word for word: EvaluatePolynomial (Chebyshev and monomial, degrees 5-31: power basis, Paterson-Stockmeyer
     recursion with backward scale propagation, relinearisations, rescales) gives the ciphertext oracle/scheme.py

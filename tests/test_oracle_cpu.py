@@ -294,3 +294,23 @@ def test_oracle_polynomial_evaluation_matches_numpy(orc):
         got = np.real(O.decode(O.decrypt(out)))
         want = C.chebval(x, c.astype(np.float64)) if cheb else np.polynomial.polynomial.polyval(x, c.astype(np.float64))
         assert np.max(np.abs(got - want)) < 1e-6, (deg, cheb)
+
+
+def test_oracle_bootstrap_refreshes_a_ciphertext(orc):
+    """a16 on the oracle (oracle/bootstrap.py restates csrc/bootstrap.cu; the word-for-word comparison with the GPU is
+    tests/test_gpu_scheme.py::test_bootstrap_words_equal_the_oracles).  Contract of LG/bootstrapper.go:61-80: a ciphertext at
+    level 1 comes back at the top level with the default scale and the same values; with sparse slots a zero-padded input
+    comes back replicated (the shim's post-factor MaxSlots/slots)."""
+    from oracle.bootstrap import OBootstrapper
+    from oracle.scheme import OScheme
+    O = OScheme(11, [55, 40, 40], [56, 56], 40, 32, 11)
+    O.gen_secret_key(); O.gen_public_key(); O.gen_relin_key()
+    rng = np.random.default_rng(8)
+    for num_slots in (1024, 128):
+        ob = OBootstrapper(O, [61, 61, 61, 61], num_slots)
+        x = np.zeros(1024); x[:num_slots] = rng.uniform(-1, 1, num_slots)
+        out = ob.bootstrap(O.encrypt(O.encode(x, 1, 2.0 ** 40)))
+        assert out.level == 2 and out.scale == 2.0 ** 40
+        got = O.decode(O.decrypt(out))
+        want = np.tile(x[:num_slots], 1024 // num_slots)
+        assert np.max(np.abs(got.real - want)) < 1e-6 * (1024 // num_slots) and np.max(np.abs(got.imag)) < 1e-6 * (1024 // num_slots)
