@@ -200,8 +200,10 @@ void FreeCArray(void* p) { std::free(p); }
 // ---------------------------------------------------------------- tensors
 void DeletePlaintext(int id) { release_tracked(S().pts, id); }
 void DeleteCiphertext(int id) { release_tracked(S().cts, id); }
-unsigned long GetPlaintextScale(int id) { return (unsigned long)PT(id).scale; }
-unsigned long GetCiphertextScale(int id) { return (unsigned long)CT(id).scale; }
+// scales above 2^64 (a product before its rescale) saturate instead of overflowing the cast
+static unsigned long scale_to_ulong(scale_t s) { return s >= 18446744073709551615.0L ? ~0ul : (s <= 0 ? 0ul : (unsigned long)s); }
+unsigned long GetPlaintextScale(int id) { return scale_to_ulong(PT(id).scale); }
+unsigned long GetCiphertextScale(int id) { return scale_to_ulong(CT(id).scale); }
 void SetPlaintextScale(int id, unsigned long scale) { PT(id).scale = (scale_t)scale; }
 void SetCiphertextScale(int id, unsigned long scale) { CT(id).scale = (scale_t)scale; }
 int GetPlaintextLevel(int id) { return PT(id).level; }
@@ -311,7 +313,8 @@ int ModDropCiphertext(int ct) { Ciphertext& c = CT(ct); OB_CHECK(c.level >= 1, "
 // ---------------------------------------------------------------- interop: raw limbs in / out (parity tests, e2e bench, multi-GPU gather)
 int B200_ImportCiphertext(const uint64_t* data, int level, int degree, double scale, int logSlots) {
     Scheme& s = S();
-    auto c = s.new_ct(level, degree, (scale_t)scale, logSlots > 0 ? logSlots : s.log_max_slots);
+    OB_CHECK(logSlots >= 0 && logSlots <= s.log_max_slots, "B200_ImportCiphertext: logSlots out of range");
+    auto c = s.new_ct(level, degree, (scale_t)scale, logSlots > 0 ? logSlots : s.log_max_slots);   // 0 = full slots
     OB_CUDA(cudaMemcpyAsync(c->data.p, data, c->data.bytes, cudaMemcpyHostToDevice, stream()));
     OB_CUDA(cudaStreamSynchronize(stream()));
     return push_ct(std::move(c));
@@ -419,16 +422,19 @@ void NewLinearTransformEvaluator(void) { S(); }
 int GenerateLinearTransform(int* diagIdx, int nIdx, float* diagData, int nData, int level, float bsgsRatio, char* ioMode) {
     Scheme& s = S();
     const int slots = 1 << s.log_max_slots;
-    OB_CHECK((long long)nData == (long long)nIdx * slots, "GenerateLinearTransform: diagData must hold nIdx * slots values");
+    // io_mode "load" (LG/lineartransform.go:76-84): the diagonals were serialized earlier and come back through
+    // LoadPlaintextDiagonal; only the plan is built here and diagData may be empty
+    const bool load = ioMode != nullptr && std::strcmp(ioMode, "load") == 0;
+    OB_CHECK(load || (long long)nData == (long long)nIdx * slots, "GenerateLinearTransform: diagData must hold nIdx * slots values");
     std::map<int, std::vector<double2>> diags;
     for (int k = 0; k < nIdx; ++k) {
         std::vector<double2>& v = diags[diagIdx[k]];
+        if (load) continue;
         v.resize(slots);
         for (int x = 0; x < slots; ++x) v[x] = make_double2((double)diagData[(size_t)k * slots + x], 0.0);
     }
     const int log_ratio = (int)std::log((double)bsgsRatio);      // natural log, as LG/lineartransform.go:67
-    (void)ioMode;   // "load" is served by LoadPlaintextDiagonal overwriting the encoded diagonals
-    return lt_push(lt_build(s, diags, level, s.q_at(level), s.log_max_slots, log_ratio));
+    return lt_push(lt_build(s, diags, level, s.q_at(level), s.log_max_slots, log_ratio, !load));
 }
 int EvaluateLinearTransform(int transform, int ct) { return op_new(true, {&CT(ct).trk}, [&] { return lt_apply(S(), lt_get(transform), CT(ct)); }); }
 void DeleteLinearTransform(int id) { settle_all(); lt_delete(id); }

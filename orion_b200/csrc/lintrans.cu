@@ -104,14 +104,14 @@ int find_best_bsgs_ratio(const std::vector<int>& diags, int slots, int log_max_r
 }
 
 std::unique_ptr<LinearTransform> lt_build(Scheme& s, const std::map<int, std::vector<double2>>& diagonals, int level,
-                                          scale_t scale, int log_slots, int log_bsgs_ratio) {
+                                          scale_t scale, int log_slots, int log_bsgs_ratio, bool encode) {
     OB_CHECK(level >= 0 && level <= s.max_level, "linear transform level out of range");
     OB_CHECK(s.nP > 0, "linear transforms need special primes (LogP)");
     auto lt = std::make_unique<LinearTransform>();
     const int slots = 1 << log_slots, N = s.N;
     lt->level = level; lt->log_slots = log_slots; lt->scale = scale; lt->W = level + 1 + s.nP;
     for (auto& kv : diagonals) {
-        OB_CHECK((int)kv.second.size() == slots, "diagonal length must equal the slot count");
+        OB_CHECK(!encode || (int)kv.second.size() == slots, "diagonal length must equal the slot count");
         lt->diag_idx.push_back(kv.first & (slots - 1));
     }
     std::sort(lt->diag_idx.begin(), lt->diag_idx.end());
@@ -125,13 +125,13 @@ std::unique_ptr<LinearTransform> lt_build(Scheme& s, const std::map<int, std::ve
     for (size_t k = 0; k < lt->babies.size(); ++k) baby_slot[lt->babies[k]] = (int)k;
 
     // encode every diagonal, pre-rotated right by its giant step, at `scale` into QP (Montgomery form)
-    lt->diags.alloc((size_t)nd * lt->W * N * 8);
+    if (encode) lt->diags.alloc((size_t)nd * lt->W * N * 8);
     const int chunk = std::max(1, std::min(nd, (int)((256u << 20) / ((size_t)lt->W * N * 8))));
     std::vector<double2> host((size_t)chunk * slots);
     DevBuf dv((size_t)chunk * slots * sizeof(double2));
     std::map<int, const std::vector<double2>*> by_idx;
     for (auto& kv : diagonals) by_idx[kv.first & (slots - 1)] = &kv.second;
-    for (int k0 = 0; k0 < nd; k0 += chunk) {
+    for (int k0 = 0; encode && k0 < nd; k0 += chunk) {
         const int nb = std::min(chunk, nd - k0);
         for (int k = 0; k < nb; ++k) {
             const int d = lt->diag_idx[k0 + k], j = ((d / lt->N1) * lt->N1) & (slots - 1);

@@ -25,7 +25,9 @@ int find_best_bsgs_ratio(const std::vector<int>& diags, int slots, int log_max_r
 
 // diagonals: idx -> slots complex values (not pre-rotated).  Encoded at `scale` into QP at `level`.
 std::unique_ptr<LinearTransform> lt_build(Scheme& s, const std::map<int, std::vector<double2>>& diagonals, int level,
-                                          scale_t scale, int log_slots, int log_bsgs_ratio);
+                                          scale_t scale, int log_slots, int log_bsgs_ratio, bool encode = true);
+// encode = false (io_mode "load", LG/lineartransform.go:76-84): the BSGS plan only, with empty diagonals that
+// LoadPlaintextDiagonal fills in later; the map's values are ignored.
 std::unique_ptr<Ciphertext> lt_apply(Scheme& s, const LinearTransform& lt, const Ciphertext& in);
 std::vector<u64> lt_galois_elements(Scheme& s, const LinearTransform& lt);
 

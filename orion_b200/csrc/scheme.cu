@@ -156,6 +156,9 @@ const EvalKey& Scheme::galois_key(u64 galEl) {
     DevBuf s_out((size_t)ctx->nmod * N * 8);
     automorphism_ntt(*ctx, sk.u(), s_out.u(), ctx->nmod, ctx->galois_index(inv));
     auto key = gen_eval_key(sk.u(), s_out.u());
+    // the key is shared by every dataflow lane: it is published only once it is complete (a lazily generated key is built on
+    // whichever lane asked for it first, and another lane could otherwise read it half written)
+    OB_CUDA(cudaStreamSynchronize(stream()));
     return *galois_keys.emplace(galEl, std::move(key)).first->second;
 }
 

@@ -149,4 +149,12 @@ def test_rotation_key_and_diagonal_blobs_roundtrip(B):
         B.LoadRotationKey(key_blobs[g], g)
     got = words(B, B.EvaluateLinearTransform(lt, ct))
     assert np.array_equal(got, want)
+    # io_mode "load" (LG/lineartransform.go:76-84): a transform created WITHOUT diagonal data -- the reference passes the
+    # index list only -- gets its diagonals from the blobs and gives the same words
+    lt2 = B.GenerateLinearTransform(diag_idx, np.zeros(0, dtype=np.float32), level, 2.0, "load")
+    assert sorted(B.GetLinearTransformRotationKeys(lt2)) == gal
+    for d in diag_idx:
+        B.LoadPlaintextDiagonal(diag_blobs[d], lt2, d)
+    assert np.array_equal(words(B, B.EvaluateLinearTransform(lt2, ct)), want)
+    B.DeleteLinearTransform(lt2)
     B.DeleteLinearTransform(lt)
