@@ -96,6 +96,13 @@ void  B200_ModDown(void* ctx, int level, const uint64_t* accQP, uint64_t* outQ);
 /* ---- rescale by the last prime (lattigo/evaluator.go:84-99; HEonGPU operator.cu:906-980) ---- */
 void B200_Rescale(void* ctx, int level, const uint64_t* in, uint64_t* out, int polys);
 void B200_RescaleDev(void* ctx, int level, const void* in, void* out, int polys);
+/* No counterpart in the reference.  The rescale of B200_RescaleDev for callers
+ * that may not allocate (CUDA graph capture, serving loops): its scratch and launch descriptors live in one static device
+ * array (32 MiB + 32 KiB per GPU, held until exit), it calls no cudaMalloc / cudaFree / pool routine, and gives the same
+ * words.  Limit: polys * (level + 1) * N <= B200_NoAllocMaxWords() (2^22); beyond it returns -1 with a message and launches
+ * nothing (0 = ok).  All calls share the array: calls that overlap on the GPU race; calls on the library's stream do not. */
+int      B200_RescaleDevNoAlloc(void* ctx, int level, const void* in, void* out, int polys);
+size_t   B200_NoAllocMaxWords(void);
 
 /* ---- element-wise limb arithmetic on n limbs (chain index = limb index): 0 add, 1 sub, 2 neg, 3 mul ---- */
 void B200_Elementwise(void* ctx, int op, const uint64_t* a, const uint64_t* b, uint64_t* out, int n);

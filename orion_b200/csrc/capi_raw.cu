@@ -23,6 +23,10 @@ void d2h(void* h, const void* d, size_t bytes) {
 cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
 }  // namespace
 
+namespace ob {
+Context& raw_context(void* handle) { return *R(handle)->ctx; }     // for noalloc.cu
+}
+
 extern "C" {
 
 int B200_GenModuli(const int* logQ, int nQ, const int* logP, int nP, int logNthRoot, uint64_t* Q, uint64_t* P) {

@@ -56,6 +56,8 @@ RAW_SIGNATURES = {
     "B200_ModDown": ([c_vp, c_int, u64p, u64p], None),
     "B200_Rescale": ([c_vp, c_int, u64p, u64p, c_int], None),
     "B200_RescaleDev": ([c_vp, c_int, c_vp, c_vp, c_int], None),
+    "B200_RescaleDevNoAlloc": ([c_vp, c_int, c_vp, c_vp, c_int], c_int),
+    "B200_NoAllocMaxWords": ([], c_sz),
     "B200_Elementwise": ([c_vp, c_int, u64p, u64p, u64p, c_int], None),
 }
 
