@@ -891,6 +891,16 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
         attr_set = true;
     }
 #define OB_IP_ARGS c1, c1_zstride, digits, dig_zstride, m, out, out_zstride
+    // ORION_B200_IP_OVERLAP=1: the integer-path launch (few limbs, multiplier-bound) goes to a side stream so it can share
+    // the GPU with the FP64-path launch (HBM-bound) instead of following it
+    static const bool overlap = [] { const char* e = std::getenv("ORION_B200_IP_OVERLAP"); return e && std::atoi(e) != 0; }();
+    StreamFork fork((overlap && nf && ni) ? 2 : 1);
+    if (ni && fork.size() > 0) {
+        fork.branch(0);
+        ProbeScope ps(PROBE_IP_INT);
+        OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), dim3(tiles, ni, n), tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        fork.branch(1);
+    }
     if (nf) {
         probe_begin(PROBE_IP_F64);
         const size_t ring = (size_t)stages * 2 * tpb * IP_SLOT_BYTES;
@@ -899,10 +909,11 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
         else OB_LAUNCH((ntt2_ip_kernel<ArithF64, 0>), dim3(tiles, nf, n), tpb, SMX, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
         probe_end(PROBE_IP_F64);
     }
-    if (ni) {
+    if (ni && fork.size() == 0) {
         ProbeScope ps(PROBE_IP_INT);
         OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), dim3(tiles, ni, n), tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
     }
+    fork.join();
 #undef OB_IP_ARGS
 }
 
