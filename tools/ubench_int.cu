@@ -1,1594 +1,70 @@
-// Integer-pipe micro-benchmark for B200 (generated by the python snippet in the commit that added it).
-// Reports thread-ops / clk / SM for the instructions a 64-bit modular butterfly is built from.
+// Integer / FP64 pipe micro-benchmark for B200: thread-ops / clk / SM of the instructions a 64-bit modular butterfly is
+// built from (results: profiles/r1_ubench_int.txt).  Every kernel runs ITERS iterations of 64 "bodies" over 8 independent
+// dependency chains per thread (8 chains x 8 repeats, fully unrolled), 2 CTAs of 1024 threads per SM.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/ubench_int tools/ubench_int.cu && tools/ubench_int
 #include <cstdio>
 #include <cuda_runtime.h>
 typedef unsigned long long u64; typedef unsigned int u32;
 constexpr int ITERS = 1024;
 
-__global__ void __launch_bounds__(1024) k_imad_wide(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_imad_lo(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u32 x0 = (u32)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u32 x1 = (u32)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u32 x2 = (u32)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u32 x3 = (u32)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u32 x4 = (u32)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u32 x5 = (u32)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u32 x6 = (u32)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u32 x7 = (u32)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_imad_hi(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u32 x0 = (u32)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u32 x1 = (u32)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u32 x2 = (u32)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u32 x3 = (u32)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u32 x4 = (u32)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u32 x5 = (u32)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u32 x6 = (u32)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u32 x7 = (u32)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_iadd3(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u32 x0 = (u32)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u32 x1 = (u32)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u32 x2 = (u32)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u32 x3 = (u32)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u32 x4 = (u32)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u32 x5 = (u32)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u32 x6 = (u32)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u32 x7 = (u32)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(x0));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(x1));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(x2));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(x3));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(x4));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(x5));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(x6));
-    asm volatile("add.u32 %0, %0, %1;" : "+r"(x7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(x7));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_add_u64(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("add.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_lop3(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u32 x0 = (u32)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u32 x1 = (u32)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u32 x2 = (u32)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u32 x3 = (u32)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u32 x4 = (u32)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u32 x5 = (u32)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u32 x6 = (u32)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u32 x7 = (u32)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x7) : "r"(a), "r"(b));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_setp_selp(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u32 x0 = (u32)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u32 x1 = (u32)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u32 x2 = (u32)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u32 x3 = (u32)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u32 x4 = (u32)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u32 x5 = (u32)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u32 x6 = (u32)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u32 x7 = (u32)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x0) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x1) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x2) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x3) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x4) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x5) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x6) : "r"(a), "r"(b));
-    asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x7) : "r"(a), "r"(b));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_pred_sub64(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x7) : "l"(a64));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_min_sub64(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x0) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x1) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x2) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x3) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x4) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x5) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x6) : "l"(a64));
-    asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x7) : "l"(a64));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_mulhi64(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_mullo64(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x0) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x1) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x2) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x3) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x4) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x5) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x6) : "l"(a64));
-    asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x7) : "l"(a64));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_dfma(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  double x0 = (double)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  double x1 = (double)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  double x2 = (double)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  double x3 = (double)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  double x4 = (double)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  double x5 = (double)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  double x6 = (double)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  double x7 = (double)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x0) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x1) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x2) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x3) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x4) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x5) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x6) : "d"(ad));
-    asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x7) : "d"(ad));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_ffma(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  float x0 = (float)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  float x1 = (float)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  float x2 = (float)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  float x3 = (float)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  float x4 = (float)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  float x5 = (float)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  float x6 = (float)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  float x7 = (float)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x0) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x1) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x2) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x3) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x4) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x5) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x6) : "f"(af));
-    asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x7) : "f"(af));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_wide_plus_iadd(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_wide_plus_2alu(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_lo_plus_iadd(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u32 x0 = (u32)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u32 x1 = (u32)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u32 x2 = (u32)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u32 x3 = (u32)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u32 x4 = (u32)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u32 x5 = (u32)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u32 x6 = (u32)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u32 x7 = (u32)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x0) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y0) : "r"(z0)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z0) : "r"(y0));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x1) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y1) : "r"(z1)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z1) : "r"(y1));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x2) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y2) : "r"(z2)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z2) : "r"(y2));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x3) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y3) : "r"(z3)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z3) : "r"(y3));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x4) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y4) : "r"(z4)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z4) : "r"(y4));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x5) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y5) : "r"(z5)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z5) : "r"(y5));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x6) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y6) : "r"(z6)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z6) : "r"(y6));
-    asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(x7) : "r"(a), "r"(b)); asm volatile("add.u32 %0, %0, %1;" : "+r"(y7) : "r"(z7)); asm volatile("add.u32 %0, %0, %1;" : "+r"(z7) : "r"(y7));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_wide_plus_lo(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y0) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y1) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y2) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y3) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y4) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y5) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y6) : "r"(a), "r"(b));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(y7) : "r"(a), "r"(b));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
-__global__ void __launch_bounds__(1024) k_dfma_plus_wide(u64* out, u32 a0, u32 b0) {
-  u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b; double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;
-  u64 x0 = (u64)(b0 + 0 + threadIdx.x); u32 y0 = 0 + a0, z0 = 0 + b0; double d0 = 1.0 + 0;
-  u64 x1 = (u64)(b0 + 1 + threadIdx.x); u32 y1 = 1 + a0, z1 = 1 + b0; double d1 = 1.0 + 1;
-  u64 x2 = (u64)(b0 + 2 + threadIdx.x); u32 y2 = 2 + a0, z2 = 2 + b0; double d2 = 1.0 + 2;
-  u64 x3 = (u64)(b0 + 3 + threadIdx.x); u32 y3 = 3 + a0, z3 = 3 + b0; double d3 = 1.0 + 3;
-  u64 x4 = (u64)(b0 + 4 + threadIdx.x); u32 y4 = 4 + a0, z4 = 4 + b0; double d4 = 1.0 + 4;
-  u64 x5 = (u64)(b0 + 5 + threadIdx.x); u32 y5 = 5 + a0, z5 = 5 + b0; double d5 = 1.0 + 5;
-  u64 x6 = (u64)(b0 + 6 + threadIdx.x); u32 y6 = 6 + a0, z6 = 6 + b0; double d6 = 1.0 + 6;
-  u64 x7 = (u64)(b0 + 7 + threadIdx.x); u32 y7 = 7 + a0, z7 = 7 + b0; double d7 = 1.0 + 7;
-  #pragma unroll 1
-  for (int it = 0; it < ITERS; ++it) {
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x0) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d0) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x1) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d1) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x2) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d2) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x3) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d3) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x4) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d4) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x5) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d5) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x6) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d6) : "d"(ad));
-    asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x7) : "r"(b)); asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d7) : "d"(ad));
-  }
-  u64 s = 0;
-  s += (u64)x0 + y0 + z0 + (u64)d0;
-  s += (u64)x1 + y1 + z1 + (u64)d1;
-  s += (u64)x2 + y2 + z2 + (u64)d2;
-  s += (u64)x3 + y3 + z3 + (u64)d3;
-  s += (u64)x4 + y4 + z4 + (u64)d4;
-  s += (u64)x5 + y5 + z5 + (u64)d5;
-  s += (u64)x6 + y6 + z6 + (u64)d6;
-  s += (u64)x7 + y7 + z7 + (u64)d7;
-  if (s == 0x123456789ull) out[threadIdx.x] = s;
-}
+#define WIDE(i) asm volatile("{.reg .u32 lo, hi; mov.b64 {lo,hi}, %0; mad.wide.u32 %0, lo, %1, %0;}" : "+l"(x[i]) : "r"(b));
+#define IADD2(i) asm volatile("add.u32 %0, %0, %1;" : "+r"(y[i]) : "r"(z[i])); asm volatile("add.u32 %0, %0, %1;" : "+r"(z[i]) : "r"(y[i]));
+#define LO(v, i) asm volatile("mad.lo.u32 %0, %1, %0, %2;" : "+r"(v[i]) : "r"(a), "r"(b));
+
+// XT: type of the x chain; BODY(i): the instruction(s) of one body on chain i
+#define UBENCH(NAME, XT, BODY)                                                                                           \
+    __global__ void __launch_bounds__(1024) NAME(u64* out, u32 a0, u32 b0) {                                             \
+        u32 a = a0 + threadIdx.x, b = b0 | 1; u64 a64 = ((u64)a << 29) | b;                                              \
+        double ad = 1.0 + 1e-9 * a; float af = 1.0f + 1e-6f * a; (void)a64; (void)ad; (void)af; (void)b;                 \
+        XT x[8]; u32 y[8], z[8]; double d[8];                                                                            \
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) { x[i] = (XT)(b0 + i + threadIdx.x); y[i] = i + a0; z[i] = i + b0; d[i] = 1.0 + i; } \
+        _Pragma("unroll 1") for (int it = 0; it < ITERS; ++it) {                                                         \
+            _Pragma("unroll") for (int r = 0; r < 8; ++r) {                                                              \
+                _Pragma("unroll") for (int i = 0; i < 8; ++i) { BODY(i) }                                                \
+            }                                                                                                            \
+        }                                                                                                                \
+        u64 s = 0;                                                                                                       \
+        _Pragma("unroll") for (int i = 0; i < 8; ++i) s += (u64)x[i] + y[i] + z[i] + (u64)d[i];                          \
+        if (s == 0x123456789ull) out[threadIdx.x] = s;                                                                   \
+    }
+
+#define B_WIDE(i) WIDE(i)
+#define B_LO(i) LO(x, i)
+#define B_HI(i) asm volatile("mad.hi.u32 %0, %1, %0, %2;" : "+r"(x[i]) : "r"(a), "r"(b));
+#define B_IADD3(i) asm volatile("add.u32 %0, %0, %1;" : "+r"(x[i]) : "r"(y[i])); asm volatile("add.u32 %0, %0, %1;" : "+r"(y[i]) : "r"(x[i]));
+#define B_ADD64(i) asm volatile("add.u64 %0, %0, %1;" : "+l"(x[i]) : "l"(a64));
+#define B_LOP3(i) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[i]) : "r"(a), "r"(b));
+#define B_SETP(i) asm volatile("{.reg .pred p; setp.ge.u32 p, %0, %1; selp.u32 %0, %2, %0, p;}" : "+r"(x[i]) : "r"(a), "r"(b));
+#define B_PSUB(i) asm volatile("{.reg .pred p; setp.ge.u64 p, %0, %1; @p sub.u64 %0, %0, %1;}" : "+l"(x[i]) : "l"(a64));
+#define B_MINSUB(i) asm volatile("{.reg .u64 t; sub.u64 t, %0, %1; min.u64 %0, %0, t;}" : "+l"(x[i]) : "l"(a64));
+#define B_MULHI(i) asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(x[i]) : "l"(a64));
+#define B_MULLO(i) asm volatile("mul.lo.u64 %0, %0, %1;" : "+l"(x[i]) : "l"(a64));
+#define B_DFMA(i) asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(x[i]) : "d"(ad));
+#define B_FFMA(i) asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(x[i]) : "f"(af));
+#define B_WIDE_IADD(i) WIDE(i) IADD2(i)
+#define B_WIDE_2ALU(i) WIDE(i) IADD2(i) IADD2(i)
+#define B_LO_IADD(i) LO(x, i) IADD2(i)
+#define B_WIDE_LO(i) WIDE(i) LO(y, i)
+#define B_DFMA_WIDE(i) WIDE(i) asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d[i]) : "d"(ad));
+
+UBENCH(k_imad_wide, u64, B_WIDE)
+UBENCH(k_imad_lo, u32, B_LO)
+UBENCH(k_imad_hi, u32, B_HI)
+UBENCH(k_iadd3, u32, B_IADD3)
+UBENCH(k_add_u64, u64, B_ADD64)
+UBENCH(k_lop3, u32, B_LOP3)
+UBENCH(k_setp_selp, u32, B_SETP)
+UBENCH(k_pred_sub64, u64, B_PSUB)
+UBENCH(k_min_sub64, u64, B_MINSUB)
+UBENCH(k_mulhi64, u64, B_MULHI)
+UBENCH(k_mullo64, u64, B_MULLO)
+UBENCH(k_dfma, double, B_DFMA)
+UBENCH(k_ffma, float, B_FFMA)
+UBENCH(k_wide_plus_iadd, u64, B_WIDE_IADD)
+UBENCH(k_wide_plus_2alu, u64, B_WIDE_2ALU)
+UBENCH(k_lo_plus_iadd, u32, B_LO_IADD)
+UBENCH(k_wide_plus_lo, u64, B_WIDE_LO)
+UBENCH(k_dfma_plus_wide, u64, B_DFMA_WIDE)
 
 template <class K> void run(const char* name, K k, u64* d) {
     int dev; cudaGetDevice(&dev); cudaDeviceProp p; cudaGetDeviceProperties(&p, dev);
@@ -1602,25 +78,12 @@ template <class K> void run(const char* name, K k, u64* d) {
     printf("%-18s %8.3f ms  %7.2f bodies/clk/SM (clock %d MHz)  %s\n", name, ms,
            bodies / (ms * 1e-3) / (clk_khz * 1e3) / p.multiProcessorCount, clk_khz / 1000, cudaGetErrorString(cudaGetLastError()));
 }
+
 int main() {
     u64* d; cudaMalloc(&d, 1024 * 8);
-    run("imad_wide", k_imad_wide, d);
-    run("imad_lo", k_imad_lo, d);
-    run("imad_hi", k_imad_hi, d);
-    run("iadd3", k_iadd3, d);
-    run("add_u64", k_add_u64, d);
-    run("lop3", k_lop3, d);
-    run("setp_selp", k_setp_selp, d);
-    run("pred_sub64", k_pred_sub64, d);
-    run("min_sub64", k_min_sub64, d);
-    run("mulhi64", k_mulhi64, d);
-    run("mullo64", k_mullo64, d);
-    run("dfma", k_dfma, d);
-    run("ffma", k_ffma, d);
-    run("wide_plus_iadd", k_wide_plus_iadd, d);
-    run("wide_plus_2alu", k_wide_plus_2alu, d);
-    run("lo_plus_iadd", k_lo_plus_iadd, d);
-    run("wide_plus_lo", k_wide_plus_lo, d);
-    run("dfma_plus_wide", k_dfma_plus_wide, d);
+#define RUN(n) run(#n, k_##n, d);
+    RUN(imad_wide) RUN(imad_lo) RUN(imad_hi) RUN(iadd3) RUN(add_u64) RUN(lop3) RUN(setp_selp) RUN(pred_sub64) RUN(min_sub64)
+    RUN(mulhi64) RUN(mullo64) RUN(dfma) RUN(ffma) RUN(wide_plus_iadd) RUN(wide_plus_2alu) RUN(lo_plus_iadd) RUN(wide_plus_lo)
+    RUN(dfma_plus_wide)
     return 0;
 }
