@@ -9,6 +9,7 @@ CPU NTT compiled in place (oracle/_ref/libgpuntt_ref.so) and returns None when i
 import ctypes
 import os
 import subprocess
+import sys
 
 import numpy as np
 
@@ -36,6 +37,9 @@ def build(force=False):
         subprocess.check_call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     if os.path.isdir("/root/reference") and (force or not os.path.exists(os.path.join(_HERE, "_ref", "libgpuntt_refgpu.so"))):
         subprocess.check_call(["make", "-C", _HERE, "refgpu"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference") and (force or not os.path.exists(os.path.join(_HERE, "_ref", "orion_pyc.zip"))):
+        # the reference's Python layer as bytecode, for the live drop-in test (tests/test_gpu_live.py)
+        subprocess.check_call([sys.executable, os.path.join(_HERE, "build_refpy.py")], stdout=subprocess.DEVNULL)
     return so
 
 

@@ -198,8 +198,11 @@ void DeleteScheme(void) {
 void FreeCArray(void* p) { std::free(p); }
 
 // ---------------------------------------------------------------- tensors
-void DeletePlaintext(int id) { release_tracked(S().pts, id); }
-void DeleteCiphertext(int id) { release_tracked(S().cts, id); }
+// After DeleteScheme the tables are gone and a late Delete* is a no-op, as in the Go shim (LG/scheme.go:89-100 resets the heaps,
+// LG/tensors.go:35-42 deletes from a map): the reference's Python objects free their handles from __del__, in any order, also
+// at interpreter exit (PY/tensors.py:16-22,112-118).
+void DeletePlaintext(int id) { if (!g_scheme) return; release_tracked(S().pts, id); }
+void DeleteCiphertext(int id) { if (!g_scheme) return; release_tracked(S().cts, id); }
 // scales above 2^64 (a product before its rescale) saturate instead of overflowing the cast
 static unsigned long scale_to_ulong(scale_t s) { return s >= 18446744073709551615.0L ? ~0ul : (s <= 0 ? 0ul : (unsigned long)s); }
 unsigned long GetPlaintextScale(int id) { return scale_to_ulong(PT(id).scale); }
@@ -437,7 +440,7 @@ int GenerateLinearTransform(int* diagIdx, int nIdx, float* diagData, int nData, 
     return lt_push(lt_build(s, diags, level, s.q_at(level), s.log_max_slots, log_ratio, !load));
 }
 int EvaluateLinearTransform(int transform, int ct) { return op_new(true, {&CT(ct).trk}, [&] { return lt_apply(S(), lt_get(transform), CT(ct)); }); }
-void DeleteLinearTransform(int id) { settle_all(); lt_delete(id); }
+void DeleteLinearTransform(int id) { if (!g_scheme) return; settle_all(); lt_delete(id); }
 ArrayResultInt GetLinearTransformRotationKeys(int transform) {
     return make_array<u64, ArrayResultInt>(lt_galois_elements(S(), lt_get(transform)));
 }

@@ -104,9 +104,8 @@ class Replayer:
         self.run(0, self.t.n_compile)
         self._snap = (dict(self.ct), dict(self.pt))
 
-    def infer(self):
-        """One encrypted inference: encode + encrypt the input, net(ct), decrypt + decode.  Returns the decoded slots.
-        Repeatable: handles created by a previous inference are released first."""
+    def reset_inference(self):
+        """Release the handles a previous inference created; back to the state right after setup()."""
         ct0, pt0 = self._snap
         for k, v in list(self.ct.items()):
             if k not in ct0 or ct0[k] != v:
@@ -115,8 +114,46 @@ class Replayer:
             if k not in pt0 or pt0[k] != v:
                 self.B.DeletePlaintext(v)
         self.ct, self.pt = dict(ct0), dict(pt0)
+
+    def infer(self):
+        """One encrypted inference: encode + encrypt the input, net(ct), decrypt + decode.  Returns the decoded slots.
+        Repeatable: handles created by a previous inference are released first."""
+        self.reset_inference()
         self.run(self.t.n_compile, len(self.t.ops))
         return self.output
+
+
+class BatchReplayer:
+    """K independent inferences (K images) over ONE scheme -- keys, encoded diagonals, polynomials and bootstrappers are
+    shared -- issued call by call in lockstep: call i of image 0, call i of image 1, ...  The images' ciphertexts are
+    independent, so the library's dataflow lanes (csrc/capi.cu) run them on different streams and the small-ring launches of
+    one image fill the SMs the others leave idle.  This is how a server would use the boundary for a batch: nothing in the
+    per-call semantics changes, every image's result is bit-identical to its single replay."""
+
+    def __init__(self, backend, trace, k, seed=1234):
+        self.rs = [Replayer(backend, trace, seed=seed) for _ in range(k)]
+        self.t = trace
+
+    def setup(self):
+        r0 = self.rs[0]
+        r0.setup()
+        for r in self.rs[1:]:
+            r.ct, r.pt, r.lt, r.poly = dict(r0.ct), dict(r0.pt), r0.lt, r0.poly
+            r._snap = (dict(r0._snap[0]), dict(r0._snap[1]))
+
+    def infer(self):
+        for r in self.rs:
+            r.reset_inference()
+        ops = self.t.ops
+        for i in range(self.t.n_compile, len(ops)):
+            op = ops[i]
+            for r in self.rs:
+                r._run(i, op)
+        return [r.output for r in self.rs]
+
+    @property
+    def counts(self):
+        return self.rs[0].counts
 
 
 def replay_model(backend, json_path, npz_path, sync=None):

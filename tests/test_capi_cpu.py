@@ -101,3 +101,14 @@ def test_bench_reference_arm_prints_exactly_one_json_line():
     assert d["value"] > 0 and d["higher_is_better"] is True
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+
+
+def test_late_deletes_without_a_scheme_are_no_ops(b200lib):
+    """The reference's Python objects free their handles from __del__ in any order, also after DeleteScheme and at interpreter
+    exit (orion/backend/python/tensors.py:16-22,112-118); the Go shim's Delete* then delete from an empty map
+    (lattigo/tensors.go:35-42).  Same here: no abort, no GPU needed."""
+    from orion_b200.bindings import B200Library
+    B = B200Library()
+    B.DeleteScheme()
+    B.DeleteCiphertext(3); B.DeletePlaintext(0); B.DeleteLinearTransform(7)
+    B.DeleteScheme()
