@@ -42,6 +42,8 @@ uint64_t B200_GaloisElement(void* ctx, int rot);            /* 5^rot mod 2N; lat
 void     B200_Sync(void);
 unsigned long long B200_LaunchCount(void);                   /* kernels launched by this library so far */
 double   B200_AlgorithmicBytes(void);          /* running sum of SURVEY 8(d) algorithmic bytes of the evaluator ops issued so far */
+double   B200_DeviceBytes(int peak);           /* device bytes held by the library's buffers now (0) or at their high-water mark (1) */
+double   B200_ReclaimedBytes(void);            /* bytes of regenerable state (Galois keys, bootstrap factor sets) dropped under memory pressure so far */
 void*    B200_Stream(void);                                  /* cudaStream_t all work is issued on */
 void     B200_TimerStart(void);                              /* CUDA events on that stream */
 float    B200_TimerStopMs(void);

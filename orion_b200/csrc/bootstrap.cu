@@ -129,7 +129,10 @@ std::map<int, std::vector<double2>> to_lt_diags(const DiagMat& m, double factor)
 
 struct Bootstrapper {
     int log_slots = 0, r = 3, K1 = 0, top_level = 0, res_levels = 0;
-    std::unique_ptr<Scheme> bs;                          // scheme over the extended chain, same secret
+    std::shared_ptr<Scheme> bs;                          // scheme over the extended chain, same secret (one per slot count; at
+                                                         // logN >= 15 ONE for all slot counts: the chain does not depend on it and a key is 0.4 GB)
+    std::vector<int> log_p;
+    int busy = 0;                                        // boot_apply in progress: its factor set is not reclaimable
     std::vector<std::unique_ptr<LinearTransform>> cts, stc;
     std::vector<DiagMat> cts_m, stc_m;                   // host factors (encoded lazily: their scales depend on the input)
     Polynomial cheb;
@@ -141,6 +144,7 @@ struct Bootstrapper {
     std::map<scale_t, Encoded> encoded;
     u64 use_clock = 0;
 };
+size_t lt_set_bytes(const std::vector<std::unique_ptr<LinearTransform>>& v) { size_t b = 0; for (auto& l : v) b += l->diags.bytes; return b; }
 std::map<int, std::unique_ptr<Bootstrapper>>& g_boot = *new std::map<int, std::unique_ptr<Bootstrapper>>();     // keyed by slot count (LG/bootstrapper.go:16)
 
 // ORION_B200_BOOT_DUMP=<dir>: every stage of a bootstrap writes its ciphertext words (and the host-side tables) there, for
@@ -188,6 +192,29 @@ std::vector<double> cheb_interp(int deg, double K1, int r) {
 
 void boot_reset() { if (!g_boot.empty()) cudaStreamSynchronize(stream()); g_boot.clear(); }
 
+// memory pressure (common.h): encoded DFT factor sets are re-encodable from the host factors -- parked sets first (LRU), then
+// the current set of every bootstrapper that is not inside boot_apply
+static size_t boot_reclaim(size_t want) {
+    size_t freed = 0;
+    while (freed < want) {
+        Bootstrapper* ob = nullptr; std::map<scale_t, Bootstrapper::Encoded>::iterator old;
+        for (auto& kv : g_boot)
+            for (auto i = kv.second->encoded.begin(); i != kv.second->encoded.end(); ++i)
+                if (!ob || i->second.last_use < old->second.last_use) { ob = kv.second.get(); old = i; }
+        if (!ob) break;
+        freed += lt_set_bytes(old->second.cts) + lt_set_bytes(old->second.stc);
+        ob->encoded.erase(old);
+    }
+    for (auto& kv : g_boot) {
+        Bootstrapper& b = *kv.second;
+        if (freed >= want) break;
+        if (b.busy || b.cts.empty()) continue;
+        freed += lt_set_bytes(b.cts) + lt_set_bytes(b.stc);
+        b.cts.clear(); b.stc.clear(); b.built_for_scale = 0;
+    }
+    return freed;
+}
+
 void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
     if (g_boot.count(num_slots)) return;                                   // cached per slot count, as the reference
     OB_CHECK(s.has_sk(), "NewBootstrapper needs the secret key (bootstrapping keys are generated here)");
@@ -216,11 +243,20 @@ void boot_new(Scheme& s, const std::vector<int>& logP, int num_slots) {
     for (int bits : logP) np[bits]++;
     for (auto& kv : np) take(kv.first, kv.second, P);
     OB_CHECK(!P.empty(), "NewBootstrapper: boot_params.LogP is empty");
-    b->bs = std::make_unique<Scheme>(s.ctx->logN, Q, P, s.params.log_scale, s.params.h, s.rng.derive(0xB007B007ull ^ (u64)num_slots));
+    static const int reclaimer = register_reclaimer(boot_reclaim); (void)reclaimer;
+    b->log_p = logP;
+    static const char* share_env = std::getenv("ORION_B200_BOOT_SHARE");
+    const bool share = share_env ? std::atoi(share_env) != 0 : s.ctx->logN >= 15;
+    if (share)
+        for (auto& kv : g_boot) if (kv.second->log_p == logP) { b->bs = kv.second->bs; break; }
+    const bool fresh = !b->bs;
+    if (fresh) b->bs = std::make_shared<Scheme>(s.ctx->logN, Q, P, s.params.log_scale, s.params.h, s.rng.derive(0xB007B007ull ^ (u64)num_slots));
     Scheme& bs = *b->bs;
-    bs.default_scale = s.default_scale;
-    bs.set_secret_key(s.sk_coeffs);
-    bs.gen_relin_key();
+    if (fresh) {
+        bs.default_scale = s.default_scale;
+        bs.set_secret_key(s.sk_coeffs);
+        bs.gen_relin_key();
+    }
     b->top_level = bs.max_level;
     std::vector<double2> roots; host_roots(2 * s.N, roots);
     b->cts_m = dft_factors(log_slots, 2 * s.N, CTS_DEPTH, true, roots);
@@ -259,6 +295,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
     OB_CHECK(it != g_boot.end(), "Bootstrap: no bootstrapper for this slot count (call NewBootstrapper)");
     OB_CHECK(in.degree == 1, "Bootstrap expects a degree-1 ciphertext");
     Bootstrapper& b = *it->second;
+    struct Busy { int& n; explicit Busy(int& x) : n(x) { ++n; } ~Busy() { --n; } } busy(b.busy);
     Scheme& bs = *b.bs;
     Context& c = *bs.ctx;
     const int N = bs.N, n_log = b.log_slots, top = b.top_level;

@@ -62,6 +62,8 @@ uint64_t B200_ContextPsi(void* h, int idx) { return R(h)->ctx->psi[idx]; }
 void B200_Sync(void) { ensure_device(); OB_CUDA(cudaDeviceSynchronize()); }        // main stream, dataflow lanes and side streams
 unsigned long long B200_LaunchCount(void) { return g_launches; }
 double B200_AlgorithmicBytes(void) { return g_alg_bytes; }
+double B200_DeviceBytes(int peak) { return (double)device_bytes(peak != 0); }
+double B200_ReclaimedBytes(void) { return (double)reclaimed_bytes(); }
 void* B200_Stream(void) { return (void*)stream(); }
 void B200_TimerStart(void) {
     if (!g_ev0) { OB_CUDA(cudaEventCreate(&g_ev0)); OB_CUDA(cudaEventCreate(&g_ev1)); }

@@ -1,5 +1,6 @@
 // common.h -- shared host-side declarations for liborion_b200.so (B200 / sm_100a CKKS backend).
 #pragma once
+#include <functional>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -126,6 +127,22 @@ bool stream_fork_enabled();      // ORION_B200_STREAMS=0 disables forking (every
 void ensure_device();           // aborts loudly when no CUDA device is usable
 
 // stream-ordered device buffer (cudaMallocAsync pool with an unlimited release threshold -> frees are cached)
+// ---- memory pressure ----
+// A logN = 16 network does not fit in 180 GB with everything resident (ResNet-20: 115 rotation keys x 595 MB, 8 381 encoded
+// diagonals = 50 GB, three bootstrappers' keys and DFT factors).  When the stream-ordered pool cannot satisfy an allocation,
+// DevBuf::alloc synchronises the device, retries, and then asks the registered reclaimers -- least-recently-used Galois keys
+// that can be regenerated from the resident secret key, encoded bootstrap factor sets that can be re-encoded -- to free memory
+// until the allocation succeeds; only when nothing is left to give back is the error fatal.  State an operation is still
+// reading on the host side is protected by OpPin: objects touched since the outermost live OpPin was taken are not evictable.
+typedef std::function<size_t(size_t want)> Reclaimer;       // frees (stream-ordered) up to ~want bytes, returns what it freed
+int register_reclaimer(Reclaimer r);
+void unregister_reclaimer(int id);
+unsigned long long use_tick();                              // monotonic use clock (LRU stamps)
+unsigned long long pin_floor();                             // stamps >= this belong to the operation in progress
+struct OpPin { OpPin(); ~OpPin(); OpPin(const OpPin&) = delete; OpPin& operator=(const OpPin&) = delete; };
+unsigned long long reclaimed_bytes();                       // diagnostics: total bytes given back under pressure
+size_t device_bytes(bool peak);                             // bytes held through DevBuf now / at their high-water mark
+
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;

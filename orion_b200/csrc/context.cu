@@ -1,6 +1,7 @@
 // context.cu -- parameter generation and HBM-resident tables.
 #include "context.h"
 #include <algorithm>
+#include <map>
 #include <unordered_map>
 #include <cuda.h>
 
@@ -211,15 +212,72 @@ void StreamFork::join() {
 // Measured and rejected: a per-stream free list in front of the pool (cudaMallocAsync / cudaFreeAsync cost 2.4 + 0.5 us
 // of host time per buffer, 52 k buffers per ResNet-20 inference).  It saved 10 ms of a 390 ms inference and held 30+ GB
 // of cached blocks over the 25 lanes and side streams, so DevBuf stays directly on the stream-ordered pool.
+namespace {
+std::map<int, Reclaimer>& reclaimers() { static auto* m = new std::map<int, Reclaimer>(); return *m; }
+int g_reclaimer_id = 0, g_pin_depth = 0;
+unsigned long long g_use_clock = 1, g_pin_floor = ~0ull, g_reclaimed = 0;
+bool g_reclaiming = false;
+size_t g_dev_bytes = 0, g_dev_peak = 0;                    // bytes currently held through DevBuf, and their high-water mark
+// ORION_B200_MEM_LIMIT_MB: treat DevBuf allocations beyond this total as out of memory (exercises the reclaim path on a small ring)
+size_t mem_limit() { static const size_t l = std::getenv("ORION_B200_MEM_LIMIT_MB") ? (size_t)std::atoll(std::getenv("ORION_B200_MEM_LIMIT_MB")) << 20 : 0; return l; }
+cudaError_t try_alloc(void** p, size_t n) {
+    if (mem_limit() && g_dev_bytes + n > mem_limit()) return cudaErrorMemoryAllocation;
+    const cudaError_t e = cudaMallocAsync(p, n, stream());
+    if (e != cudaSuccess) cudaGetLastError();
+    return e;
+}
+}
+int register_reclaimer(Reclaimer r) { reclaimers()[++g_reclaimer_id] = std::move(r); return g_reclaimer_id; }
+void unregister_reclaimer(int id) { reclaimers().erase(id); }
+unsigned long long use_tick() { return ++g_use_clock; }
+unsigned long long pin_floor() { return g_pin_depth ? g_pin_floor : ~0ull; }
+unsigned long long reclaimed_bytes() { return g_reclaimed; }
+size_t device_bytes(bool peak) { return peak ? g_dev_peak : g_dev_bytes; }
+OpPin::OpPin() { if (g_pin_depth++ == 0) g_pin_floor = ++g_use_clock; }
+OpPin::~OpPin() { --g_pin_depth; }
+
+// the pool is out of memory: device-wide synchronisation (frees queued on any lane complete, nothing in flight reads what is
+// about to be evicted), retry; then evict through the reclaimers, a few GB at a time, until the allocation fits
+static void* alloc_under_pressure(size_t n) {
+    void* p = nullptr;
+    OB_CHECK(!g_reclaiming, "out of device memory while reclaiming");
+    g_reclaiming = true;
+    static const bool verbose = std::getenv("ORION_B200_DEBUG") != nullptr;
+    for (int round = 0; round < 64; ++round) {
+        OB_CUDA(cudaDeviceSynchronize());
+        if (try_alloc(&p, n) == cudaSuccess) { g_reclaiming = false; return p; }
+        const size_t want = std::max<size_t>(n + (n >> 2), mem_limit() ? mem_limit() / 8 : (size_t)6 << 30);
+        size_t freed = 0;
+        for (auto& kv : reclaimers()) { if (freed >= want) break; freed += kv.second(want - freed); }
+        g_reclaimed += freed;
+        if (verbose) std::fprintf(stderr, "[mem] allocation of %.2f GB failed: reclaimed %.2f GB (round %d)\n", n / 1073741824.0, freed / 1073741824.0, round);
+        if (freed == 0) {
+            // last resort: hand the pool's unused blocks back to the driver so that it can re-map them into one range
+            cudaMemPool_t pool; int dev = 0;
+            OB_CUDA(cudaGetDevice(&dev)); OB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+            OB_CUDA(cudaDeviceSynchronize());
+            OB_CUDA(cudaMemPoolTrimTo(pool, 0));
+            if (try_alloc(&p, n) == cudaSuccess) { g_reclaiming = false; return p; }
+            break;
+        }
+    }
+    g_reclaiming = false;
+    size_t fr = 0, tot = 0; cudaMemGetInfo(&fr, &tot);
+    OB_FATAL("CUDA error: out of memory allocating " + std::to_string(n >> 20) + " MiB (device free " + std::to_string(fr >> 20) + " of " +
+             std::to_string(tot >> 20) + " MiB, nothing left to reclaim)");
+    return nullptr;
+}
 void DevBuf::alloc(size_t n) {
     release();
     if (n == 0) return;
     OB_HP("cudaMallocAsync");
-    OB_CUDA(cudaMallocAsync(&p, n, stream()));
-    bytes = n;
+    const cudaError_t e = try_alloc(&p, n);
+    if (e == cudaErrorMemoryAllocation) p = alloc_under_pressure(n);
+    else OB_CUDA(e);
+    bytes = n; g_dev_bytes += n; if (g_dev_bytes > g_dev_peak) g_dev_peak = g_dev_bytes;
 }
 void DevBuf::release() {
-    if (p) { OB_HP("cudaFreeAsync"); cudaFreeAsync(p, g_cur ? g_cur : g_stream); p = nullptr; bytes = 0; }
+    if (p) { OB_HP("cudaFreeAsync"); cudaFreeAsync(p, g_cur ? g_cur : g_stream); p = nullptr; g_dev_bytes -= bytes; bytes = 0; }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -455,6 +513,35 @@ const BaseConv& Context::base_conv(const std::vector<int>& src, const std::vecto
     upload(bc->inv, inv); upload(bc->mat, mat); upload(bc->negvq, negvq);
     upload(bc->half_src, hs); upload(bc->half_dst, hd);
     upload(bc->mat_d, matd); upload(bc->negvq_d, negd);
+    static const bool tc = std::getenv("ORION_B200_BC_TC") && std::atoi(std::getenv("ORION_B200_BC_TC")) != 0;
+    if (tc && ns <= 8) {
+        // Tensor-core trial.  y_i = sum_a y_{i,a} 2^(8a) (bytes), so
+        //   sum_i y_i M[i][t] = sum_{(i,a)} y_{i,a} W[i][a][t] (mod p_t),  W[i][a][t] = M[i][t] 2^(8a) mod p_t  (Montgomery form kept),
+        // and with W split into bytes b the contraction is 8 (or 4) exact u8 x u8 -> s32 GEMM columns per destination:
+        //   S_b[x][t] = sum_{(i,a)} y_{i,a}[x] * byte_b(W[i][a][t]) <= 64 * 255^2 < 2^22,   out = REDC(sum_b S_b 2^(8b)).
+        // Column c of n8-tile tau of destination block blk holds (t, b) = (4 blk + (c >> 1), 2 tau + (c & 1)), so that after the
+        // MMAs lane j of a quad owns all eight byte sums of destination 4 blk + j.  K index: chunk ch, lane-quad position jB,
+        // register half -> (i, a) = (jB + 4 ch, 0..3 | 4..7), matching the A fragments the kernel builds from the words of y.
+        const int nblk = (nd + 3) / 4;
+        std::vector<uint32_t> fr((size_t)nblk * 4 * 2 * 32 * 2, 0u);
+        for (int blk = 0; blk < nblk; ++blk)
+            for (int tau = 0; tau < 4; ++tau)
+                for (int ch = 0; ch < 2; ++ch)
+                    for (int lane = 0; lane < 32; ++lane) {
+                        const int col = lane >> 2, jb = lane & 3, t = 4 * blk + (col >> 1), b = 2 * tau + (col & 1), i = jb + 4 * ch;
+                        if (t >= nd || i >= ns) continue;
+                        const u64 p = mod[dst[t]];
+                        u64 w = mat[(size_t)i * nd + t];
+                        uint32_t r[2] = {0u, 0u};
+                        for (int a = 0; a < 8; ++a) {
+                            r[a >> 2] |= (uint32_t)((w >> (8 * b)) & 0xFF) << (8 * (a & 3));
+                            w = mulmod_u64(w, 256 % p, p);
+                        }
+                        const size_t o = ((((size_t)blk * 4 + tau) * 2 + ch) * 32 + lane) * 2;
+                        fr[o] = r[0]; fr[o + 1] = r[1];
+                    }
+        upload(bc->tc_frag, fr);
+    }
     return *bc_cache_.emplace(std::move(key), std::move(bc)).first->second;
 }
 

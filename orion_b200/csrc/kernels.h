@@ -34,7 +34,7 @@ void from_montgomery(Context& c, const u64* in, u64* out, int polys, int limbs, 
 // destination limb as the UNREDUCED sum of centred residues in double form (|value| <= (1 + 0.7 ns) q): the forward NTT
 // that always follows reads it as its lazy input (LimbDesc::aux bit 0) -- saves the final reduction here and the
 // word->double conversion there.  ns <= 4 keeps the NTT's growth bound (ntt.cu) intact.
-inline bool bc_raw_out(bool f64_src, int ns, int dst_bits) { return f64_src && ns <= 4 && dst_bits <= 46; }
+__host__ __device__ inline bool bc_raw_out(bool f64_src, int ns, int dst_bits) { return f64_src && ns <= 4 && dst_bits <= 46; }
 struct BaseConvPlan { const BaseConv* bc = nullptr; const LimbDesc* out_off = nullptr; };
 BaseConvPlan make_baseconv_plan(Context& c, const std::vector<int>& src, const std::vector<int>& dst,
                                 const std::vector<int>& out_off);
@@ -47,8 +47,10 @@ struct BcDev {
     const ulonglong2* inv; const u64* mat; const u64* negvq; const u64* half_src; const u64* half_dst;
     const double* mat_d; const double* negvq_d; int f64_src;
     int mm;                       // integer-path accumulation mode of this conversion (ks_kernels.cu: 0 / 1 raw / 2 96-bit)
+    const uint2* tc_frag;         // tensor-core trial: B fragments (context.cu base_conv), nullptr when not built
 };
-struct BaseConvBatch { const BcDev* dev = nullptr; int n = 0; size_t smem = 0; int max_ns = 0; int min_nd = 1 << 30; int mac_mode = 0; };
+struct BaseConvBatch { const BcDev* dev = nullptr; int n = 0; size_t smem = 0; int max_ns = 0; int min_nd = 1 << 30; int mac_mode = 0;
+                       bool tc_ok = false; int max_nd = 0; };
 BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& plans, const std::vector<int>& in_off,
                                   const std::vector<int>& out_base);
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered);

@@ -240,6 +240,129 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     }
 }
 
+// ---- INT8 tensor-core trial of the base-conversion contraction (north star: "tried ... kept only if ncu shows a gain") ----
+// Same words as baseconv_batch_kernel<false, 8, *, *> on conversions with ns <= 8 sources (used for batches that hold a digit of
+// 5..8 sources: the ModUp of the bootstrapping chain; shorter last digits ride along zero-padded).  A warp owns RT tiles of 16 coefficients; lane (g, j) = (lane >> 2, lane & 3) computes y_i for the sources
+// i in {j, j + 4} and the rows {g, g + 8} of each tile -- exactly the 32-bit halves its A fragments of mma.m16n8k32.u8 need -- and
+// the overflow estimate v from the quad's quotients summed in source order (bit-identical with the scalar kernel).  Per block of
+// four destinations: 4 (2 when all four are below 2^32) n8 tiles x 2 K-chunks of MMAs against the precomputed B fragments
+// (context.cu base_conv), then lane j recombines the eight exact byte sums of destination 4 blk + j into a 79-bit integer,
+// reduces it with one REDC and adds -v Q.  Off unless ORION_B200_BC_TC=1.
+__device__ __forceinline__ void mma_u8(int (&c)[4], const uint32_t (&a)[4], const uint2 b) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+}
+constexpr int TC_TPB = 128;
+template <int RT, bool CENTERED>
+__global__ void __launch_bounds__(TC_TPB)
+baseconv_tc_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
+                   const ModConst* __restrict__ mc) {
+    OB_PDL_SYNC();
+    const BcDev d = descs[blockIdx.y];
+    const int ns = d.ns, nd = d.nd;
+    const int nblk = (nd + 3) >> 2, bchunk = (nblk + gridDim.z - 1) / gridDim.z;
+    const int blk0 = blockIdx.z * bchunk, blk1 = min(nblk, blk0 + bchunk);
+    if (blk0 >= blk1) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, j = lane & 3;
+    const int xbase = (blockIdx.x * (TC_TPB / 32) + warp) * (16 * RT);
+    uint32_t a[RT][2][4];
+    int v[RT][2];
+    {
+        u64 sq[2], sw[2], swp[2], sh[2]; double sqd[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int i = j + 4 * h;
+            sq[h] = 1; sw[h] = swp[h] = sh[h] = 0; sqd[h] = 1.0;
+            if (i < ns) {
+                const ModConst& m = mc[d.src_mod[i]]; sq[h] = m.q; sqd[h] = m.qd; const ulonglong2 w = d.inv[i]; sw[h] = w.x; swp[h] = w.y;
+                if (CENTERED) sh[h] = d.half_src[i];
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RT; ++r) {
+            double quo[2][2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int rr = 0; rr < 2; ++rr) {
+                    const int i = j + 4 * h, x = xbase + r * 16 + g + 8 * rr;
+                    u64 y = 0;
+                    if (i < ns) {
+                        u64 xi = in[(size_t)(d.in_off + i) * N + x];
+                        if (CENTERED) xi = add_mod(xi, sh[h], sq[h]);
+                        y = shoup_mul(xi, sw[h], swp[h], sq[h]);
+                    }
+                    a[r][h][rr] = (uint32_t)y; a[r][h][2 + rr] = (uint32_t)(y >> 32);
+                    quo[h][rr] = __ddiv_rn(__ull2double_rn(y), sqd[h]);
+                }
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+                double vf = 0.0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const double t = __shfl_sync(0xffffffffu, quo[i >> 2][rr], (lane & ~3) | (i & 3));
+                    if (i < ns) vf = __dadd_rn(vf, t);
+                }
+                v[r][rr] = (ns == 1 && !CENTERED) ? 0 : (int)vf;        // a single source is a plain copy + reduction
+            }
+        }
+    }
+    for (int blk = blk0; blk < blk1; ++blk) {
+        const int t = 4 * blk + j;
+        const bool valid = t < nd;
+        u64 q = 3, qi = 0, dh = 0; int off = 0;
+        bool raw = false;                // bc_raw_out(): the NTT that follows reads this limb as a lazy double (kernels.h)
+        if (valid) {
+            const ModConst& m = mc[d.dst_mod[t]]; q = m.q; qi = m.qinv_neg; off = d.out_base + (int)d.out_off[t].in_off;
+            raw = !CENTERED && bc_raw_out(d.f64_src != 0, ns, m.bits);
+            if (CENTERED) dh = d.half_dst[t];
+        }
+        const bool small = __all_sync(0xffffffffu, (q >> 32) == 0);
+        int c[RT][4][4];
+#pragma unroll
+        for (int r = 0; r < RT; ++r)
+#pragma unroll
+            for (int tau = 0; tau < 4; ++tau)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) c[r][tau][e] = 0;
+        const uint2* fr = d.tc_frag + (size_t)blk * (4 * 2 * 32) + lane;
+#pragma unroll
+        for (int tau = 0; tau < 4; ++tau) {
+            if (tau < 2 || !small) {
+#pragma unroll
+                for (int ch = 0; ch < 2; ++ch) {
+                    const uint2 b = __ldg(fr + (tau * 2 + ch) * 32);
+#pragma unroll
+                    for (int r = 0; r < RT; ++r) mma_u8(c[r][tau], a[r][ch], b);
+                }
+            }
+        }
+        if (valid) {
+#pragma unroll
+            for (int r = 0; r < RT; ++r)
+#pragma unroll
+                for (int rr = 0; rr < 2; ++rr) {
+                    // byte sums S_b = c[r][b >> 1][2 rr + (b & 1)], each below 2^22
+                    const u64 A = (u64)(uint32_t)c[r][0][2 * rr] + ((u64)(uint32_t)c[r][0][2 * rr + 1] << 8) +
+                                  ((u64)(uint32_t)c[r][1][2 * rr] << 16) + ((u64)(uint32_t)c[r][1][2 * rr + 1] << 24);
+                    u64 lo = A, hi = 0;
+                    if (!small) {
+                        const u64 B = (u64)(uint32_t)c[r][2][2 * rr] + ((u64)(uint32_t)c[r][2][2 * rr + 1] << 8) +
+                                      ((u64)(uint32_t)c[r][3][2 * rr] << 16) + ((u64)(uint32_t)c[r][3][2 * rr + 1] << 24);
+                        lo = A + (B << 32);
+                        hi = (B >> 32) + (lo < A);
+                    }
+                    u64 res = mont_redc(hi, lo, q, qi);
+                    res = add_mod(res, __ldg(&d.negvq[(size_t)t * (ns + 1) + v[r][rr]]), q);
+                    if (CENTERED) res = sub_mod(res, dh, q);
+                    if (raw) res = (u64)__double_as_longlong(__ull2double_rn(res));
+                    out[(size_t)off * N + xbase + r * 16 + g + 8 * rr] = res;
+                }
+        }
+    }
+}
+
 // acc[c][t][x] (+)= sum_j dig_j[t][x] * evk[j][c][chain(t)][x]   (evk Montgomery form)
 template <bool GATHER, bool ACCUM>
 __global__ void __launch_bounds__(TPB)
@@ -385,7 +508,10 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
         const BaseConv& bc = *plans[z].bc;
         h[z] = BcDev{bc.ns, bc.nd, in_off[z], out_base[z], bc.src_mod.as<int>(), bc.dst_mod.as<int>(), plans[z].out_off,
                      bc.inv.as<ulonglong2>(), bc.mat.u(), bc.negvq.u(), bc.half_src.u(), bc.half_dst.u(),
-                     bc.mat_d.as<double>(), bc.negvq_d.as<double>(), bc.f64_src ? 1 : 0, 0};
+                     bc.mat_d.as<double>(), bc.negvq_d.as<double>(), bc.f64_src ? 1 : 0, 0,
+                     bc.tc_frag.p ? bc.tc_frag.as<uint2>() : nullptr};
+        b.tc_ok = (z == 0 || b.tc_ok) && bc.tc_frag.p != nullptr;
+        b.max_nd = std::max(b.max_nd, bc.nd);
         const size_t ns = bc.ns, nd = bc.nd;
         const size_t sm = 8 * (2 * (ns * nd + nd * (ns + 1)) + 4 * nd + 2 * ns + ns + (ns & 1)) + 16 * ns + 8 * nd + 16;
         b.smem = std::max(b.smem, sm);
@@ -409,6 +535,22 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
 
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered) {
     if (b.n == 0) return;
+    if (b.tc_ok && b.max_ns >= 5) {                   // tensor-core path (ORION_B200_BC_TC=1): batches with 5..8-source conversions
+        static const int rt = std::getenv("ORION_B200_BC_TC_RT") ? std::atoi(std::getenv("ORION_B200_BC_TC_RT")) : 2;
+        static const int zw = std::getenv("ORION_B200_BC_TC_Z") ? std::atoi(std::getenv("ORION_B200_BC_TC_Z")) : 6;
+        const int rows = 16 * rt * (TC_TPB / 32);
+        if (c.N % rows == 0) {
+            const long ctas = (long)(c.N / rows) * b.n;
+            const int nblk = (b.max_nd + 3) / 4;
+            const int zsplit = (int)std::min<long>(std::max<long>(1, (148L * zw + ctas - 1) / ctas), std::max(1, nblk / 2));
+            dim3 grid(c.N / rows, b.n, zsplit);
+#define OB_TC(RTV) do { if (centered) OB_LAUNCH((baseconv_tc_kernel<RTV, true>), grid, TC_TPB, 0, stream(), in, out, c.N, b.dev, c.dmc()); \
+                        else OB_LAUNCH((baseconv_tc_kernel<RTV, false>), grid, TC_TPB, 0, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+            if (rt == 1) OB_TC(1); else if (rt == 4) OB_TC(4); else OB_TC(2);
+#undef OB_TC
+            return;
+        }
+    }
     OB_CHECK(b.smem <= 48 * 1024, "base conversion tables exceed the static shared-memory window");
     // size the launch for >= ~2 CTAs of work per SM: one coefficient per thread and the destination limbs split over
     // gridDim.z when the ring is small, two coefficients per thread and no split when it is large

@@ -163,6 +163,7 @@ std::vector<u64> lt_galois_elements(Scheme& s, const LinearTransform& lt) {
 
 std::unique_ptr<Ciphertext> lt_apply(Scheme& s, const LinearTransform& lt, const Ciphertext& in) {
     OB_HP("lt_apply (total)");
+    OpPin pin;                                                  // the Galois keys collected below stay resident until the launches are queued
     OB_CHECK(lt.has_data(), "linear transform has no encoded diagonals (removed?)");
     OB_CHECK(in.degree == 1, "EvaluateLinearTransform expects a degree-1 ciphertext");
     Context& c = *s.ctx;

@@ -63,8 +63,24 @@ void Scheme::init_common(const SchemeRng& rng_) {
     N = ctx->N; nQ = ctx->nQ; nP = ctx->nP; max_level = nQ - 1; log_max_slots = ctx->logN - 1;
     default_scale = std::ldexp((scale_t)1, params.log_scale);
     rng = rng_;
+    reclaimer_id = register_reclaimer([this](size_t want) { return reclaim_galois_keys(want); });
+}
+size_t Scheme::reclaim_galois_keys(size_t want) {
+    if (!has_sk()) return 0;                                  // loaded keys without the secret key cannot be rebuilt
+    size_t freed = 0;
+    const unsigned long long floor = pin_floor();
+    while (freed < want) {
+        auto old = galois_keys.end();
+        for (auto i = galois_keys.begin(); i != galois_keys.end(); ++i)
+            if (i->second->last_use < floor && (old == galois_keys.end() || i->second->last_use < old->second->last_use)) old = i;
+        if (old == galois_keys.end()) break;
+        freed += old->second->data.bytes;
+        galois_keys.erase(old);
+    }
+    return freed;
 }
 Scheme::~Scheme() {
+    unregister_reclaimer(reclaimer_id);
     cudaStreamSynchronize(stream());
     drop_scheme_tables(*ctx);
 }
@@ -147,7 +163,7 @@ void Scheme::gen_relin_key() {
 
 const EvalKey& Scheme::galois_key(u64 galEl) {
     auto it = galois_keys.find(galEl);
-    if (it != galois_keys.end()) return *it->second;
+    if (it != galois_keys.end()) { it->second->last_use = use_tick(); return *it->second; }
     OB_CHECK(has_sk(), "Galois key generation needs a secret key");
     // key switches s -> sigma_g^-1(s); the automorphism sigma_g applied afterwards maps it back to s
     u64 inv = 1, twoN = 2ull * N;
@@ -159,6 +175,7 @@ const EvalKey& Scheme::galois_key(u64 galEl) {
     // the key is shared by every dataflow lane: it is published only once it is complete (a lazily generated key is built on
     // whichever lane asked for it first, and another lane could otherwise read it half written)
     OB_CUDA(cudaStreamSynchronize(stream()));
+    key->last_use = use_tick();
     return *galois_keys.emplace(galEl, std::move(key)).first->second;
 }
 

@@ -29,7 +29,7 @@ struct Ciphertext {
     Track trk;
     u64* poly(int p, int N) const { return data.u() + (size_t)p * (level + 1) * N; }
 };
-struct EvalKey { DevBuf data; };   // [beta(max level)][2][nQ+nP][N], NTT domain, Montgomery form
+struct EvalKey { DevBuf data; unsigned long long last_use = 0; };   // [beta(max level)][2][nQ+nP][N], NTT domain, Montgomery form; LRU stamp (common.h: memory pressure)
 
 // smallest-free-integer handle table: the semantics of LG/minheap.go:27-98
 template <class T>
@@ -91,6 +91,8 @@ class Scheme {
     const EvalKey& galois_key(u64 galEl);           // generated on demand (LG/evaluator.go:34-46)
     bool has_galois_key(u64 galEl) const { return galois_keys.count(galEl) != 0; }
     void drop_galois_keys() { galois_keys.clear(); }
+    size_t reclaim_galois_keys(size_t want);        // under memory pressure: drop LRU keys (regenerated on next use; needs the secret key)
+    int reclaimer_id = 0;
     // gadget key switching skIn -> skOut; sk_in / sk_out are [nQ+nP][N] NTT polynomials
     std::unique_ptr<EvalKey> gen_eval_key(const u64* sk_in, const u64* sk_out);
 

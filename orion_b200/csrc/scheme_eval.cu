@@ -176,6 +176,7 @@ void Scheme::rescale(const Ciphertext& a, Ciphertext& out) {
 void Scheme::automorphism(const Ciphertext& a, u64 galEl, Ciphertext& out) {
     OB_CHECK(a.degree == 1, "automorphism expects a degree-1 ciphertext");
     const int L = a.level + 1;
+    OpPin pin;
     const EvalKey& key = galois_key(galEl);
     DevBuf ks((size_t)2 * L * N * 8);
     pev->keyswitch(a.level, a.poly(1, N), key.data.u(), a.data.u(), L, 1, ks.u(), L);

@@ -26,6 +26,8 @@ RAW_SIGNATURES = {
     "B200_Sync": ([], None),
     "B200_LaunchCount": ([], ctypes.c_ulonglong),
     "B200_AlgorithmicBytes": ([], ctypes.c_double),
+    "B200_ReclaimedBytes": ([], ctypes.c_double),
+    "B200_DeviceBytes": ([c_int], ctypes.c_double),
     "B200_Stream": ([], c_vp),
     "B200_TimerStart": ([], None),
     "B200_TimerStopMs": ([], ctypes.c_float),
