@@ -43,6 +43,7 @@ void     B200_Sync(void);
 unsigned long long B200_LaunchCount(void);                   /* kernels launched by this library so far */
 double   B200_AlgorithmicBytes(void);          /* running sum of SURVEY 8(d) algorithmic bytes of the evaluator ops issued so far */
 double   B200_DeviceBytes(int peak);           /* device bytes held by the library's buffers now (0) or at their high-water mark (1) */
+void     B200_TrimPool(void);                  /* synchronise and hand the pool's unused blocks back to the driver (before another process needs the GPU's memory) */
 double   B200_ReclaimedBytes(void);            /* bytes of regenerable state (Galois keys, bootstrap factor sets) dropped under memory pressure so far */
 void*    B200_Stream(void);                                  /* cudaStream_t all work is issued on */
 void     B200_TimerStart(void);                              /* CUDA events on that stream */

@@ -63,6 +63,12 @@ void B200_Sync(void) { ensure_device(); OB_CUDA(cudaDeviceSynchronize()); }     
 unsigned long long B200_LaunchCount(void) { return g_launches; }
 double B200_AlgorithmicBytes(void) { return g_alg_bytes; }
 double B200_DeviceBytes(int peak) { return (double)device_bytes(peak != 0); }
+void B200_TrimPool(void) {
+    ensure_device();
+    cudaMemPool_t pool; int dev = 0;
+    OB_CUDA(cudaDeviceSynchronize()); OB_CUDA(cudaGetDevice(&dev)); OB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    OB_CUDA(cudaMemPoolTrimTo(pool, 0));
+}
 double B200_ReclaimedBytes(void) { return (double)reclaimed_bytes(); }
 void* B200_Stream(void) { return (void*)stream(); }
 void B200_TimerStart(void) {

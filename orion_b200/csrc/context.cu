@@ -513,9 +513,9 @@ const BaseConv& Context::base_conv(const std::vector<int>& src, const std::vecto
     upload(bc->inv, inv); upload(bc->mat, mat); upload(bc->negvq, negvq);
     upload(bc->half_src, hs); upload(bc->half_dst, hd);
     upload(bc->mat_d, matd); upload(bc->negvq_d, negd);
-    static const bool tc = std::getenv("ORION_B200_BC_TC") && std::atoi(std::getenv("ORION_B200_BC_TC")) != 0;
+    static const bool tc = !(std::getenv("ORION_B200_BC_TC") && std::atoi(std::getenv("ORION_B200_BC_TC")) == 0);   // on by default
     if (tc && ns <= 8) {
-        // Tensor-core trial.  y_i = sum_a y_{i,a} 2^(8a) (bytes), so
+        // INT8 tensor-core contraction (ORION_B200_BC_TC=0 falls back to the scalar kernel).  y_i = sum_a y_{i,a} 2^(8a) (bytes), so
         //   sum_i y_i M[i][t] = sum_{(i,a)} y_{i,a} W[i][a][t] (mod p_t),  W[i][a][t] = M[i][t] 2^(8a) mod p_t  (Montgomery form kept),
         // and with W split into bytes b the contraction is 8 (or 4) exact u8 x u8 -> s32 GEMM columns per destination:
         //   S_b[x][t] = sum_{(i,a)} y_{i,a}[x] * byte_b(W[i][a][t]) <= 64 * 255^2 < 2^22,   out = REDC(sum_b S_b 2^(8b)).

@@ -30,8 +30,8 @@ struct BaseConv {
     DevBuf mat_d, negvq_d;        // double[ns][nd], double[nd][ns+1]: the same constants in standard form, as exact
                                   // doubles (FP64 contraction for destinations of at most 46 bits)
     bool f64_src = false;         // every source prime has at most 46 bits
-    DevBuf tc_frag;               // uint2[ceil(nd/4)][4][2][32]: INT8 tensor-core trial (ks_kernels.cu baseconv_tc_kernel), the
-                                  // matrix as per-lane B fragments of mma.m16n8k32.u8; built only under ORION_B200_BC_TC=1, ns <= 8
+    DevBuf tc_frag;               // uint2[ceil(nd/4)][4][2][32]: INT8 tensor-core contraction (ks_kernels.cu baseconv_tc_kernel), the
+                                  // matrix as per-lane B fragments of mma.m16n8k32.u8; for ns <= 8 unless ORION_B200_BC_TC=0
     std::vector<int> h_src, h_dst;
 };
 

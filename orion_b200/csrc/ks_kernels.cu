@@ -240,14 +240,15 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
     }
 }
 
-// ---- INT8 tensor-core trial of the base-conversion contraction (north star: "tried ... kept only if ncu shows a gain") ----
+// ---- INT8 tensor-core base-conversion contraction (north star: "tried ... kept only if ncu shows a gain" -- it does: DESIGN.md 7) ----
 // Same words as baseconv_batch_kernel<false, 8, *, *> on conversions with ns <= 8 sources (used for batches that hold a digit of
 // 5..8 sources: the ModUp of the bootstrapping chain; shorter last digits ride along zero-padded).  A warp owns RT tiles of 16 coefficients; lane (g, j) = (lane >> 2, lane & 3) computes y_i for the sources
 // i in {j, j + 4} and the rows {g, g + 8} of each tile -- exactly the 32-bit halves its A fragments of mma.m16n8k32.u8 need -- and
 // the overflow estimate v from the quad's quotients summed in source order (bit-identical with the scalar kernel).  Per block of
 // four destinations: 4 (2 when all four are below 2^32) n8 tiles x 2 K-chunks of MMAs against the precomputed B fragments
 // (context.cu base_conv), then lane j recombines the eight exact byte sums of destination 4 blk + j into a 79-bit integer,
-// reduces it with one REDC and adds -v Q.  Off unless ORION_B200_BC_TC=1.
+// reduces it with one REDC and adds -v Q.  CENTERED: the ModDown variant (+ Q/2 on the way in, - Q/2 on the way out).
+// On by default; ORION_B200_BC_TC=0 restores the scalar kernel.
 __device__ __forceinline__ void mma_u8(int (&c)[4], const uint32_t (&a)[4], const uint2 b) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
@@ -535,7 +536,7 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
 
 void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* out, bool centered) {
     if (b.n == 0) return;
-    if (b.tc_ok && b.max_ns >= 5) {                   // tensor-core path (ORION_B200_BC_TC=1): batches with 5..8-source conversions
+    if (b.tc_ok && b.max_ns >= 5) {                   // tensor-core path (ORION_B200_BC_TC=0 disables): batches with 5..8-source conversions
         static const int rt = std::getenv("ORION_B200_BC_TC_RT") ? std::atoi(std::getenv("ORION_B200_BC_TC_RT")) : 2;
         static const int zw = std::getenv("ORION_B200_BC_TC_Z") ? std::atoi(std::getenv("ORION_B200_BC_TC_Z")) : 6;
         const int rows = 16 * rt * (TC_TPB / 32);

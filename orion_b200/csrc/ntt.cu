@@ -437,21 +437,25 @@ __global__ void __launch_bounds__(1 << (LOG_E_CONTIG - 3))
 ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restrict__ digits, size_t dig_zstride,
                const IpMulti m, u64* __restrict__ out, size_t out_zstride, const __grid_constant__ LimbTab tab,
                int L, int K, int nQ, int nmod, int beta, const ModConst* __restrict__ mc,
-               const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN) {
+               const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN, int nzx) {
     OB_PDL_SYNC();
     constexpr int EPT = 8, SM_WORDS = (1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3)), TPB_ = 1 << (LOG_E_CONTIG - 3);
+    // nzx > 1: the ciphertext index is the FASTEST-varying part of blockIdx.x, so the nzx CTAs that work on the same tile of the
+    // same limb -- and, in a batch that shares one evaluation key, read the same 2 beta key tiles -- are resident together and the
+    // key comes from DRAM once per group instead of once per ciphertext (the rest are L2 hits)
+    const int bx = blockIdx.x / nzx;
     extern __shared__ __align__(16) unsigned char ip_smem[];
     u64 (*sm)[SM_WORDS] = (u64 (*)[SM_WORDS])ip_smem;                        // [2][SM_WORDS] exchange tiles
     unsigned char* ring = ip_smem + 2 * SM_WORDS * 8;                        // [STAGES][2][TPB_] slots of IP_SLOT_BYTES
     typedef typename A::T T;
-    const int t = tab.t[blockIdx.y], z = blockIdx.z, W = L + K;
+    const int t = tab.t[blockIdx.y], z = blockIdx.z + blockIdx.x % nzx, W = L + K;
     const size_t N = (size_t)1 << logN;
     const int ci = t < L ? t : nQ + (t - L);
     const A ar(mc[ci]);
     const int own = t < L ? t / K : -1;
     const typename A::TW* tw;
     if constexpr (sizeof(typename A::TW) == 8) tw = twd_all + (size_t)ci * N; else tw = tw_all + (size_t)ci * N;
-    const size_t off = ((size_t)blockIdx.x << LOG_E_CONTIG) + threadIdx.x * EPT;      // this thread's 8 words in the limb
+    const size_t off = ((size_t)bx << LOG_E_CONTIG) + threadIdx.x * EPT;      // this thread's 8 words in the limb
     const u64* __restrict__ evk = m.evk[z] + (size_t)ci * N + off;
     const u64* __restrict__ c1t = c1 + (size_t)z * c1_zstride + (size_t)t * N + off;
     const u64* __restrict__ dz = digits + (size_t)z * dig_zstride + (size_t)t * N;
@@ -461,7 +465,7 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
     int buf = 0;
     // L2 prefetch, one 128-byte line per thread: the key tiles of digit j (2 x 8 KB; direct-load variant only) and the tile
     // of digit j+1 (8 KB), so that the loads that follow the butterflies find their lines in L2
-    const size_t line = ((size_t)blockIdx.x << LOG_E_CONTIG) + (threadIdx.x & 63) * 16;
+    const size_t line = ((size_t)bx << LOG_E_CONTIG) + (threadIdx.x & 63) * 16;
     const u64* pf_evk = m.evk[z] + ((size_t)(threadIdx.x >> 6) * nmod + ci) * N + line;
     const u64* pf_dig = dz + line;
     auto stage_keys = [&](int j) {               // copies of digit j's key words into ring slot j % STAGES (empty group past the end)
@@ -894,24 +898,28 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
     // ORION_B200_IP_OVERLAP=1: the integer-path launch (few limbs, multiplier-bound) goes to a side stream so it can share
     // the GPU with the FP64-path launch (HBM-bound) instead of following it
     static const bool overlap = [] { const char* e = std::getenv("ORION_B200_IP_OVERLAP"); return e && std::atoi(e) != 0; }();
+    // CTA order: ciphertext index fastest (ORION_B200_IP_ZFAST=0 restores tile-fastest with the ciphertext in blockIdx.z)
+    static const bool zfast = [] { const char* e = std::getenv("ORION_B200_IP_ZFAST"); return !(e && std::atoi(e) == 0); }();
+    const int nzx = zfast ? n : 1;
+    const dim3 gf(tiles * nzx, nf, zfast ? 1 : n), gi(tiles * nzx, ni, zfast ? 1 : n);
     StreamFork fork((overlap && nf && ni) ? 2 : 1);
     if (ni && fork.size() > 0) {
         fork.branch(0);
         ProbeScope ps(PROBE_IP_INT);
-        OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), dim3(tiles, ni, n), tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), gi, tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
         fork.branch(1);
     }
     if (nf) {
         probe_begin(PROBE_IP_F64);
         const size_t ring = (size_t)stages * 2 * tpb * IP_SLOT_BYTES;
-        if (stages == 3) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 3>), dim3(tiles, nf, n), tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
-        else if (stages == 2) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 2>), dim3(tiles, nf, n), tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
-        else OB_LAUNCH((ntt2_ip_kernel<ArithF64, 0>), dim3(tiles, nf, n), tpb, SMX, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        if (stages == 3) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 3>), gf, tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
+        else if (stages == 2) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 2>), gf, tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
+        else OB_LAUNCH((ntt2_ip_kernel<ArithF64, 0>), gf, tpb, SMX, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
         probe_end(PROBE_IP_F64);
     }
     if (ni && fork.size() == 0) {
         ProbeScope ps(PROBE_IP_INT);
-        OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), dim3(tiles, ni, n), tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN);
+        OB_LAUNCH((ntt2_ip_kernel<ArithInt, 0>), gi, tpb, SMX, stream(), OB_IP_ARGS, ti, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
     }
     fork.join();
 #undef OB_IP_ARGS

@@ -77,6 +77,9 @@ size_t Scheme::reclaim_galois_keys(size_t want) {
         freed += old->second->data.bytes;
         galois_keys.erase(old);
     }
+    if (std::getenv("ORION_B200_DEBUG"))
+        std::fprintf(stderr, "[mem] scheme %p (nQ %d): dropped %.2f GB of Galois keys, %zu keys left (pin floor %llu)\n", (void*)this, nQ,
+                     freed / 1073741824.0, galois_keys.size(), floor);
     return freed;
 }
 Scheme::~Scheme() {

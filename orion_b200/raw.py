@@ -27,6 +27,7 @@ RAW_SIGNATURES = {
     "B200_LaunchCount": ([], ctypes.c_ulonglong),
     "B200_AlgorithmicBytes": ([], ctypes.c_double),
     "B200_ReclaimedBytes": ([], ctypes.c_double),
+    "B200_TrimPool": ([], None),
     "B200_DeviceBytes": ([c_int], ctypes.c_double),
     "B200_Stream": ([], c_vp),
     "B200_TimerStart": ([], None),

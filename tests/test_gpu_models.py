@@ -69,6 +69,23 @@ def test_resnet20_encrypted_inference_matches_cleartext(b200lib):
     assert mae < 0.02, (mae, fhe, clear)
 
 
+def test_resnet20_at_logn16_matches_cleartext(b200lib):
+    """BASELINE configs[3]: the same network with LogN forced to 16 (32768 slots, 23 linear transforms with up to 900 diagonals,
+    12 sparse-slot bootstraps at 16384 / 8192 / 4096 slots, 115 rotation keys of 595 MB): 160 GB of keys, encoded diagonals and
+    bootstrap factors, so it runs in a process of its own (tools/resnet16.py) after this one has returned its pooled memory.
+    Gate: max |FHE - exact cleartext network| <= 1e-3 on the logits (north star), same argmax."""
+    import json, subprocess, sys
+    b200lib.load().B200_TrimPool()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "resnet16.py"), "1"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    print("resnet20 logN=16: %.2f s/image, setup %.1f s, max err %.2e, peak %.0f GB, dropped under pressure %.1f GB"
+          % (res["s_per_image"], res["setup_s"], res["numerics"]["max_abs_err"], res["peak_device_gb"], res["reclaimed_under_pressure_gb"]))
+    assert res["counts"]["Bootstrap"] == 12 and res["counts"]["EvaluateLinearTransform"] == 23 and res["counts"]["EvaluatePolynomial"] == 57
+    assert res["numerics"]["max_abs_err"] <= 1e-3 and res["numerics"]["argmax_equal"], res
+
+
 def test_lola_encrypted_inference_matches_cleartext(b200lib):
     """LoLA CNN with configs/lola2.yml (logN=14, 7+2 limbs, Standard ring): same MAE gate as the reference's MLP test."""
     res = run_trace("lola")
