@@ -63,12 +63,6 @@ void B200_Sync(void) { ensure_device(); OB_CUDA(cudaDeviceSynchronize()); }     
 unsigned long long B200_LaunchCount(void) { return g_launches; }
 double B200_AlgorithmicBytes(void) { return g_alg_bytes; }
 double B200_DeviceBytes(int peak) { return (double)device_bytes(peak != 0); }
-void B200_TrimPool(void) {
-    ensure_device();
-    cudaMemPool_t pool; int dev = 0;
-    OB_CUDA(cudaDeviceSynchronize()); OB_CUDA(cudaGetDevice(&dev)); OB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
-    OB_CUDA(cudaMemPoolTrimTo(pool, 0));
-}
 double B200_ReclaimedBytes(void) { return (double)reclaimed_bytes(); }
 void* B200_Stream(void) { return (void*)stream(); }
 void B200_TimerStart(void) {
@@ -190,6 +184,48 @@ void B200_KeySwitchBatchDev(void* h, int level, int n, const void* cts, int has_
                        has_c0 ? base : nullptr, 2 * L, (u64*)out);
 }
 
+// Streams, events and device staging slots of the host-buffer pipeline below: created on first use on the current device,
+// resized when a larger ring comes along, released by B200_TrimPool (and re-created on the next call).
+struct HostPipe {
+    static constexpr int NBUF = 4;
+    cudaStream_t s_up = nullptr, s_down = nullptr;
+    cudaEvent_t up_done[NBUF], comp_done[NBUF], down_done[NBUF], start = nullptr;
+    size_t slot_words = 0;
+    void* d_in[NBUF]; void* d_out[NBUF];
+    void ensure(size_t words) {
+        if (!s_up) {
+            OB_CUDA(cudaStreamCreateWithFlags(&s_up, cudaStreamNonBlocking));
+            OB_CUDA(cudaStreamCreateWithFlags(&s_down, cudaStreamNonBlocking));
+            OB_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+            for (int i = 0; i < NBUF; ++i) {
+                OB_CUDA(cudaEventCreateWithFlags(&up_done[i], cudaEventDisableTiming));
+                OB_CUDA(cudaEventCreateWithFlags(&comp_done[i], cudaEventDisableTiming));
+                OB_CUDA(cudaEventCreateWithFlags(&down_done[i], cudaEventDisableTiming));
+            }
+        }
+        if (slot_words < words) {                           // plain cudaMalloc: the slots are used from three streams
+            release_slots();
+            for (int i = 0; i < NBUF; ++i) { OB_CUDA(cudaMalloc(&d_in[i], words * 8)); OB_CUDA(cudaMalloc(&d_out[i], words * 8)); }
+            slot_words = words;
+        }
+    }
+    void release_slots() {
+        if (!slot_words) return;
+        OB_CUDA(cudaDeviceSynchronize());
+        for (int i = 0; i < NBUF; ++i) { OB_CUDA(cudaFree(d_in[i])); OB_CUDA(cudaFree(d_out[i])); }
+        slot_words = 0;
+    }
+};
+static HostPipe& g_host_pipe = *new HostPipe();
+
+void B200_TrimPool(void) {
+    ensure_device();
+    g_host_pipe.release_slots();
+    cudaMemPool_t pool; int dev = 0;
+    OB_CUDA(cudaDeviceSynchronize()); OB_CUDA(cudaGetDevice(&dev)); OB_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+    OB_CUDA(cudaMemPoolTrimTo(pool, 0));
+}
+
 // ---- batched key switch on HOST buffers, pipelined: upload of group g+1 (copy stream), key switch of group g (compute
 //      stream) and download of group g-1 (second copy stream) overlap, so the batch runs at max(H2D, compute, D2H) per
 //      ciphertext instead of their sum.  ct_in[i] is [2][L][N] (c0 then c1; out = KeySwitch(c1) + (c0, 0)) when
@@ -202,34 +238,16 @@ void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in
     const size_t in_words = has_c0 ? 2 * LN : LN;
     // ciphertexts per pipeline stage: the first upload and the last download are not overlapped with anything, so small
     // stages shorten the fill/drain of the pipeline; compute has ~2x headroom over PCIe even at 2 per launch sequence
-    constexpr int NBUF = 4;
+    constexpr int NBUF = HostPipe::NBUF;
     static const int GROUP = [] { const char* e = std::getenv("ORION_B200_E2E_GROUP"); int g = e ? std::atoi(e) : 2; return g < 1 ? 1 : (g > 8 ? 8 : g); }();
-    static cudaStream_t s_up = nullptr, s_down = nullptr;
-    static cudaEvent_t up_done[NBUF], comp_done[NBUF], down_done[NBUF];
-    static size_t slot_words = 0;
-    static void* d_in[NBUF]; static void* d_out[NBUF];
-    if (!s_up) {
-        OB_CUDA(cudaStreamCreateWithFlags(&s_up, cudaStreamNonBlocking));
-        OB_CUDA(cudaStreamCreateWithFlags(&s_down, cudaStreamNonBlocking));
-        for (int i = 0; i < NBUF; ++i) {
-            OB_CUDA(cudaEventCreateWithFlags(&up_done[i], cudaEventDisableTiming));
-            OB_CUDA(cudaEventCreateWithFlags(&comp_done[i], cudaEventDisableTiming));
-            OB_CUDA(cudaEventCreateWithFlags(&down_done[i], cudaEventDisableTiming));
-        }
-    }
-    if (slot_words < GROUP * 2 * LN) {                      // (re)size the staging slots; plain cudaMalloc: used from 3 streams
-        OB_CUDA(cudaDeviceSynchronize());
-        for (int i = 0; i < NBUF; ++i) {
-            if (slot_words) { OB_CUDA(cudaFree(d_in[i])); OB_CUDA(cudaFree(d_out[i])); }
-            OB_CUDA(cudaMalloc(&d_in[i], GROUP * 2 * LN * 8)); OB_CUDA(cudaMalloc(&d_out[i], GROUP * 2 * LN * 8));
-        }
-        slot_words = GROUP * 2 * LN;
-    }
-    cudaEvent_t start;                                      // the copy streams must not run ahead of work already queued
-    OB_CUDA(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
-    OB_CUDA(cudaEventRecord(start, stream()));
-    OB_CUDA(cudaStreamWaitEvent(s_up, start, 0));
-    OB_CUDA(cudaStreamWaitEvent(s_down, start, 0));
+    HostPipe& hp = g_host_pipe;
+    hp.ensure((size_t)GROUP * 2 * LN);
+    cudaStream_t s_up = hp.s_up, s_down = hp.s_down;
+    cudaEvent_t* up_done = hp.up_done; cudaEvent_t* comp_done = hp.comp_done; cudaEvent_t* down_done = hp.down_done;
+    void** d_in = hp.d_in; void** d_out = hp.d_out;
+    OB_CUDA(cudaEventRecord(hp.start, stream()));            // the copy streams must not run ahead of work already queued
+    OB_CUDA(cudaStreamWaitEvent(s_up, hp.start, 0));
+    OB_CUDA(cudaStreamWaitEvent(s_down, hp.start, 0));
     int g = 0;
     for (int i0 = 0, m = 0; i0 < n; i0 += m, ++g) {
         // single ciphertexts at both ends of the batch (shortest possible un-overlapped upload / download), GROUP in between
@@ -250,7 +268,6 @@ void B200_KeySwitchBatch(void* h, int level, int n, const uint64_t* const* ct_in
     }
     OB_CUDA(cudaStreamSynchronize(s_down));
     OB_CUDA(cudaStreamSynchronize(stream()));
-    OB_CUDA(cudaEventDestroy(start));
 }
 
 // ---- pieces of the key switch, for stage-by-stage parity ----

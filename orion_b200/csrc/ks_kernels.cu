@@ -255,16 +255,41 @@ __device__ __forceinline__ void mma_u8(int (&c)[4], const uint32_t (&a)[4], cons
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
 constexpr int TC_TPB = 128;
+struct TcDst { u64 q, qi, dh; int off, raw; };          // per destination: modulus, -q^-1, Q/2 mod q (centred), output limb, raw-double flag
+// shared memory of a CTA that covers nb destination blocks: B fragments [nb][8][32] uint2, TcDst [nb*4], -vQ table [nb*4][9]
+__host__ __device__ inline size_t tc_smem_bytes(int nb) { return (size_t)nb * (8 * 32 * 8 + 4 * sizeof(TcDst) + 4 * 9 * 8); }
 template <int RT, bool CENTERED>
 __global__ void __launch_bounds__(TC_TPB)
 baseconv_tc_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                    const ModConst* __restrict__ mc) {
     OB_PDL_SYNC();
+    extern __shared__ __align__(16) unsigned char tc_smem[];
     const BcDev d = descs[blockIdx.y];
     const int ns = d.ns, nd = d.nd;
     const int nblk = (nd + 3) >> 2, bchunk = (nblk + gridDim.z - 1) / gridDim.z;
     const int blk0 = blockIdx.z * bchunk, blk1 = min(nblk, blk0 + bchunk);
     if (blk0 >= blk1) return;
+    const int nb = blk1 - blk0;
+    uint2* s_frag = (uint2*)tc_smem;
+    TcDst* s_dst = (TcDst*)(s_frag + (size_t)bchunk * 256);
+    u64* s_neg = (u64*)(s_dst + (size_t)bchunk * 4);
+    // stage this CTA's share of the conversion: one coalesced pass, overlapped with the source loads below
+    for (int i = threadIdx.x; i < nb * 256; i += TC_TPB) s_frag[i] = __ldg(d.tc_frag + (size_t)blk0 * 256 + i);
+    for (int i = threadIdx.x; i < nb * 4; i += TC_TPB) {
+        const int t = 4 * blk0 + i;
+        TcDst e{3, 0, 0, -1, 0};
+        if (t < nd) {
+            const ModConst& m = mc[d.dst_mod[t]];
+            e.q = m.q; e.qi = m.qinv_neg; e.off = d.out_base + (int)d.out_off[t].in_off;
+            e.raw = (!CENTERED && bc_raw_out(d.f64_src != 0, ns, m.bits)) ? 1 : 0;      // the NTT that follows reads a lazy double (kernels.h)
+            if (CENTERED) e.dh = d.half_dst[t];
+        }
+        s_dst[i] = e;
+    }
+    for (int i = threadIdx.x; i < nb * 4 * (ns + 1); i += TC_TPB) {
+        const int tt = i / (ns + 1), vv = i - tt * (ns + 1), t = 4 * blk0 + tt;
+        s_neg[tt * 9 + vv] = t < nd ? d.negvq[(size_t)t * (ns + 1) + vv] : 0;
+    }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, j = lane & 3;
     const int xbase = (blockIdx.x * (TC_TPB / 32) + warp) * (16 * RT);
     uint32_t a[RT][2][4];
@@ -309,37 +334,32 @@ baseconv_tc_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, con
             }
         }
     }
-    for (int blk = blk0; blk < blk1; ++blk) {
-        const int t = 4 * blk + j;
-        const bool valid = t < nd;
-        u64 q = 3, qi = 0, dh = 0; int off = 0;
-        bool raw = false;                // bc_raw_out(): the NTT that follows reads this limb as a lazy double (kernels.h)
-        if (valid) {
-            const ModConst& m = mc[d.dst_mod[t]]; q = m.q; qi = m.qinv_neg; off = d.out_base + (int)d.out_off[t].in_off;
-            raw = !CENTERED && bc_raw_out(d.f64_src != 0, ns, m.bits);
-            if (CENTERED) dh = d.half_dst[t];
-        }
-        const bool small = __all_sync(0xffffffffu, (q >> 32) == 0);
+    __syncthreads();
+    for (int b = 0; b < nb; ++b) {
+        const TcDst e = s_dst[b * 4 + j];
+        const bool valid = e.off >= 0;
+        const bool small = __all_sync(0xffffffffu, (e.q >> 32) == 0);
         int c[RT][4][4];
 #pragma unroll
         for (int r = 0; r < RT; ++r)
 #pragma unroll
             for (int tau = 0; tau < 4; ++tau)
 #pragma unroll
-                for (int e = 0; e < 4; ++e) c[r][tau][e] = 0;
-        const uint2* fr = d.tc_frag + (size_t)blk * (4 * 2 * 32) + lane;
+                for (int k = 0; k < 4; ++k) c[r][tau][k] = 0;
+        const uint2* fr = s_frag + (size_t)b * 256 + lane;
 #pragma unroll
         for (int tau = 0; tau < 4; ++tau) {
             if (tau < 2 || !small) {
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch) {
-                    const uint2 b = __ldg(fr + (tau * 2 + ch) * 32);
+                    const uint2 bf = fr[(tau * 2 + ch) * 32];
 #pragma unroll
-                    for (int r = 0; r < RT; ++r) mma_u8(c[r][tau], a[r][ch], b);
+                    for (int r = 0; r < RT; ++r) mma_u8(c[r][tau], a[r][ch], bf);
                 }
             }
         }
         if (valid) {
+            const u64* neg = s_neg + (b * 4 + j) * 9;
 #pragma unroll
             for (int r = 0; r < RT; ++r)
 #pragma unroll
@@ -354,11 +374,11 @@ baseconv_tc_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, con
                         lo = A + (B << 32);
                         hi = (B >> 32) + (lo < A);
                     }
-                    u64 res = mont_redc(hi, lo, q, qi);
-                    res = add_mod(res, __ldg(&d.negvq[(size_t)t * (ns + 1) + v[r][rr]]), q);
-                    if (CENTERED) res = sub_mod(res, dh, q);
-                    if (raw) res = (u64)__double_as_longlong(__ull2double_rn(res));
-                    out[(size_t)off * N + xbase + r * 16 + g + 8 * rr] = res;
+                    u64 res = mont_redc(hi, lo, e.q, e.qi);
+                    res = add_mod(res, neg[v[r][rr]], e.q);
+                    if (CENTERED) res = sub_mod(res, e.dh, e.q);
+                    if (e.raw) res = (u64)__double_as_longlong(__ull2double_rn(res));
+                    out[(size_t)e.off * N + xbase + r * 16 + g + 8 * rr] = res;
                 }
         }
     }
@@ -540,13 +560,14 @@ void base_convert_batch(Context& c, const BaseConvBatch& b, const u64* in, u64* 
         static const int rt = std::getenv("ORION_B200_BC_TC_RT") ? std::atoi(std::getenv("ORION_B200_BC_TC_RT")) : 2;
         static const int zw = std::getenv("ORION_B200_BC_TC_Z") ? std::atoi(std::getenv("ORION_B200_BC_TC_Z")) : 6;
         const int rows = 16 * rt * (TC_TPB / 32);
-        if (c.N % rows == 0) {
+        const int nblk = (b.max_nd + 3) / 4;
+        if (c.N % rows == 0 && tc_smem_bytes(nblk) <= 48 * 1024) {
             const long ctas = (long)(c.N / rows) * b.n;
-            const int nblk = (b.max_nd + 3) / 4;
             const int zsplit = (int)std::min<long>(std::max<long>(1, (148L * zw + ctas - 1) / ctas), std::max(1, nblk / 2));
             dim3 grid(c.N / rows, b.n, zsplit);
-#define OB_TC(RTV) do { if (centered) OB_LAUNCH((baseconv_tc_kernel<RTV, true>), grid, TC_TPB, 0, stream(), in, out, c.N, b.dev, c.dmc()); \
-                        else OB_LAUNCH((baseconv_tc_kernel<RTV, false>), grid, TC_TPB, 0, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
+            const size_t sm = tc_smem_bytes((nblk + zsplit - 1) / zsplit);
+#define OB_TC(RTV) do { if (centered) OB_LAUNCH((baseconv_tc_kernel<RTV, true>), grid, TC_TPB, sm, stream(), in, out, c.N, b.dev, c.dmc()); \
+                        else OB_LAUNCH((baseconv_tc_kernel<RTV, false>), grid, TC_TPB, sm, stream(), in, out, c.N, b.dev, c.dmc()); } while (0)
             if (rt == 1) OB_TC(1); else if (rt == 4) OB_TC(4); else OB_TC(2);
 #undef OB_TC
             return;

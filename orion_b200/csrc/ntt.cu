@@ -498,7 +498,7 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
             for (int e = 0; e < EPT; ++e) d[e] = ar.from_word(w[e]);
         } else {
             ntt_body<A, LOG_E_CONTIG, K2_BITS, false, true, true, true>(ar, sm[buf], dz + (size_t)j * W * N, nullptr, tw,
-                                                                         make_ulonglong2(0, 0), logN, d);
+                                                                         make_ulonglong2(0, 0), logN, d, false, nullptr, bx);
             buf ^= 1;
         }
         u64 k[EPT];

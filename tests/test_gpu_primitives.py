@@ -221,3 +221,14 @@ def test_cluster_ntt_switch_gives_the_same_words():
     r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "tests/test_gpu_primitives.py", "tests/test_gpu_refgpu.py",
                         "-k", "ntt_roundtrip or ntt_words or rescale or keyswitch_stages"], cwd=root, env=env, capture_output=True, text=True)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("setting", [{"ORION_B200_BC_TC": "0"}, {"ORION_B200_BC_TC": "1", "ORION_B200_BC_TC_RT": "1"},
+                                     {"ORION_B200_BC_TC": "1", "ORION_B200_BC_TC_RT": "4", "ORION_B200_BC_TC_Z": "1"},
+                                     {"ORION_B200_IP_ZFAST": "0"}])
+def test_tensor_core_base_conversion_and_cta_order_switches_give_the_oracles_words(setting):
+    """ORION_B200_BC_TC=0 forces the scalar base-conversion kernel, =1 (the default) the INT8 tensor-core contraction
+    (csrc/ks_kernels.cu baseconv_tc_kernel, plain and centred) with 1 / 2 / 4 coefficient tiles per warp and with / without the
+    destination split; ORION_B200_IP_ZFAST=0 restores the tile-fastest CTA order of the fused inner product.  Read once per
+    process, so the base-conversion and key-switch cases (chains with 5-8 special primes, partial digits) run in a child process."""
+    _rerun(setting, "baseconv or keyswitch_stages or batchdev")

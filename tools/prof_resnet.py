@@ -8,7 +8,8 @@ from orion_b200.replay import Replayer, Trace
 lib = raw.load()
 gold = os.path.join(ROOT, "tests", "golden")
 B = B200Library(); B.B200_SetSeed(42)
-t = Trace(os.path.join(gold, "trace_resnet20.json"), os.path.join(gold, "trace_resnet20.npz"))
+name = os.environ.get("TRACE", "resnet20")             # TRACE=resnet20_logn16 for the logN=16 variant
+t = Trace(os.path.join(gold, "trace_%s.json" % name), os.path.join(gold, "trace_%s.npz" % name))
 r = Replayer(B, t, seed=1234)
 r.setup(); lib.B200_Sync()
 print("setup_launches", lib.B200_LaunchCount(), flush=True)
