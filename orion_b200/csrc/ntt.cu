@@ -74,6 +74,9 @@ struct ArithInt {
     typedef ulonglong2 Acc;                              // fused inner product: 128-bit lazy accumulator (x = low, y = high < q)
     u64 q, q2, qinv_neg;
     __device__ __forceinline__ explicit ArithInt(const ModConst& m) : q(m.q), q2(2 * m.q), qinv_neg(m.qinv_neg) {}
+    static constexpr int IP_MIN_CTAS = 3;                // fused inner product: resident CTAs per SM the register allocation aims for
+    typedef u64 D;                                       // multiply-accumulate operand (a transformed digit word)
+    __device__ __forceinline__ D mac_operand(T d) const { return d; }
     __device__ __forceinline__ Acc acc_zero() const { return make_ulonglong2(0, 0); }
     __device__ __forceinline__ T keep(T x) const { return final_fwd(x); }
     __device__ __forceinline__ u64 kept_word(T x) const { return x; }
@@ -111,6 +114,9 @@ struct ArithF64 {
     typedef double Acc;                                  // fused inner product: sum of centred residues (|sum| < beta * 0.7q)
     double q, qinv, rinv;
     __device__ __forceinline__ explicit ArithF64(const ModConst& m) : q(m.qd), qinv(m.qinv_d), rinv(m.rinv_d) {}
+    static constexpr int IP_MIN_CTAS = 4;
+    typedef double D;
+    __device__ __forceinline__ D mac_operand(T d) const { return d; }
     __device__ __forceinline__ Acc acc_zero() const { return 0.0; }
     __device__ __forceinline__ T keep(T x) const { recentre(x); return x; }
     __device__ __forceinline__ u64 kept_word(T x) const { return to_word(x); }
@@ -160,6 +166,32 @@ struct ArithF64 {
     }
     __device__ __forceinline__ u64 final_fwd(T x) const { recentre(x); return to_word(x); }
     __device__ __forceinline__ u64 final_inv(T x, ulonglong2 ni) const { return to_word(mulmod(x, from_word(ni.x))); }
+};
+
+// ArithF64 butterflies with the inner product's multiply-accumulate on the INTEGER pipe (ORION_B200_IP_IMAC): the fused kernel is
+// FP64-pipe-bound (67 % busy) and a third of its FP64 work is the 8-operation modular MAC; here the transformed digit (an exact
+// centred integer, |d| <= q/2 after keep(), [0,q) for own-digit words) is shifted to (0, 2q) once per digit and multiplied
+// into a 96-bit lazy accumulator with three IMAD.WIDE (d < 2^47, Montgomery key word < 2^46: 8 digits stay below 2^96), one
+// REDC at the end -- the same word the FP64 accumulation produces.
+struct ArithF64I : ArithF64 {
+    struct Acc { u64 lo; uint32_t hi; };
+    typedef u64 D;
+    u64 qi, qinv_neg;
+    __device__ __forceinline__ explicit ArithF64I(const ModConst& m) : ArithF64(m), qi(m.q), qinv_neg(m.qinv_neg) {}
+    __device__ __forceinline__ Acc acc_zero() const { return Acc{0ull, 0u}; }
+    __device__ __forceinline__ D mac_operand(T d) const {
+        const long long di = __double_as_longlong(__dadd_rn(d, F64_MAGIC)) - __double_as_longlong(F64_MAGIC);   // exact for |d| < 2^51
+        return (u64)(di + (long long)qi);
+    }
+    __device__ __forceinline__ void mac(Acc& a, D du, u64 k) const {
+        const uint32_t d0 = (uint32_t)du, d1 = (uint32_t)(du >> 32), k0 = (uint32_t)k, k1 = (uint32_t)(k >> 32);
+        const u64 p00 = (u64)d0 * k0;
+        const u64 mid = (u64)d0 * k1 + (u64)d1 * k0;                    // < 2^48
+        const u64 add = p00 + (mid << 32);
+        a.lo += add;
+        a.hi += (uint32_t)(mid >> 32) + d1 * k1 + (uint32_t)(add < p00) + (uint32_t)(a.lo < add);
+    }
+    __device__ __forceinline__ u64 acc_word(Acc a) const { return mont_redc((u64)a.hi, a.lo, qi, qinv_neg); }
 };
 
 // One butterfly stage of a radix-2^NB round on EPT>>NB independent groups held in v[] (compile-time stage index I).
@@ -433,7 +465,7 @@ __device__ __forceinline__ void lds128(const void* p, u64& a, u64& b) {
     asm volatile("ld.shared.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "r"(s));
 }
 template <class A, int STAGES>
-__global__ void __launch_bounds__(1 << (LOG_E_CONTIG - 3))
+__global__ void __launch_bounds__(1 << (LOG_E_CONTIG - 3), A::IP_MIN_CTAS)
 ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restrict__ digits, size_t dig_zstride,
                const IpMulti m, u64* __restrict__ out, size_t out_zstride, const __grid_constant__ LimbTab tab,
                int L, int K, int nQ, int nmod, int beta, const ModConst* __restrict__ mc,
@@ -501,6 +533,9 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
                                                                          make_ulonglong2(0, 0), logN, d, false, nullptr, bx);
             buf ^= 1;
         }
+        typename A::D dd[EPT];
+#pragma unroll
+        for (int e = 0; e < EPT; ++e) dd[e] = ar.mac_operand(d[e]);
         u64 k[EPT];
         if (STAGES > 0) {
             cp_async_wait<(STAGES > 0 ? STAGES - 1 : 0)>();
@@ -509,20 +544,20 @@ ntt2_ip_kernel(const u64* __restrict__ c1, size_t c1_zstride, const u64* __restr
 #pragma unroll
             for (int c = 0; c < 4; ++c) lds128(s0 + 16 * c, k[2 * c], k[2 * c + 1]);
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) ar.mac(a0[e], d[e], k[e]);
+            for (int e = 0; e < EPT; ++e) ar.mac(a0[e], dd[e], k[e]);
 #pragma unroll
             for (int c = 0; c < 4; ++c) lds128(s1 + 16 * c, k[2 * c], k[2 * c + 1]);
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) ar.mac(a1[e], d[e], k[e]);
+            for (int e = 0; e < EPT; ++e) ar.mac(a1[e], dd[e], k[e]);
         } else {
             const u64* k0 = evk + (size_t)j * 2 * nmod * N;
             const u64* k1 = k0 + (size_t)nmod * N;
             ld_global_256(k0, k[0], k[1], k[2], k[3]); ld_global_256(k0 + 4, k[4], k[5], k[6], k[7]);
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) ar.mac(a0[e], d[e], k[e]);
+            for (int e = 0; e < EPT; ++e) ar.mac(a0[e], dd[e], k[e]);
             ld_global_256(k1, k[0], k[1], k[2], k[3]); ld_global_256(k1 + 4, k[4], k[5], k[6], k[7]);
 #pragma unroll
-            for (int e = 0; e < EPT; ++e) ar.mac(a1[e], d[e], k[e]);
+            for (int e = 0; e < EPT; ++e) ar.mac(a1[e], dd[e], k[e]);
         }
     }
     u64* o0 = out + (size_t)z * out_zstride + (size_t)t * N + off;
@@ -899,6 +934,7 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
     // the GPU with the FP64-path launch (HBM-bound) instead of following it
     static const bool overlap = [] { const char* e = std::getenv("ORION_B200_IP_OVERLAP"); return e && std::atoi(e) != 0; }();
     // CTA order: ciphertext index fastest (ORION_B200_IP_ZFAST=0 restores tile-fastest with the ciphertext in blockIdx.z)
+    static const bool imac = [] { const char* e = std::getenv("ORION_B200_IP_IMAC"); return e && std::atoi(e) != 0; }();
     static const bool zfast = [] { const char* e = std::getenv("ORION_B200_IP_ZFAST"); return !(e && std::atoi(e) == 0); }();
     const int nzx = zfast ? n : 1;
     const dim3 gf(tiles * nzx, nf, zfast ? 1 : n), gi(tiles * nzx, ni, zfast ? 1 : n);
@@ -914,6 +950,7 @@ void ks_ntt2_inner_product(Context& c, int level, int n, const u64* c1, size_t c
         const size_t ring = (size_t)stages * 2 * tpb * IP_SLOT_BYTES;
         if (stages == 3) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 3>), gf, tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
         else if (stages == 2) OB_LAUNCH((ntt2_ip_kernel<ArithF64, 2>), gf, tpb, SMX + ring, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
+        else if (imac) OB_LAUNCH((ntt2_ip_kernel<ArithF64I, 0>), gf, tpb, SMX, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
         else OB_LAUNCH((ntt2_ip_kernel<ArithF64, 0>), gf, tpb, SMX, stream(), OB_IP_ARGS, tf, L, K, c.nQ, c.nmod, beta, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN, nzx);
         probe_end(PROBE_IP_F64);
     }
