@@ -91,6 +91,12 @@ inline void launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
 // griddepcontrol.launch_dependents: the dependent grid may start launching once every CTA of this grid got here;
 // griddepcontrol.wait: block until the grid this one depends on has completed (memory visible).
 #define OB_PDL_SYNC() do { asm volatile("griddepcontrol.launch_dependents;"); asm volatile("griddepcontrol.wait;" ::: "memory"); } while (0)
+// The two halves on their own: a kernel may read what NO KERNEL writes -- launch descriptors, per-modulus constants, conversion
+// matrices (host-built tables, uploaded by memcpy before any launch that uses them) -- between OB_PDL_LAUNCH and OB_PDL_WAIT,
+// so that the dependent loads of its prologue overlap the tail of its predecessor; everything a kernel may have produced
+// (ciphertext limbs, scratch) is touched only after OB_PDL_WAIT.
+#define OB_PDL_LAUNCH() asm volatile("griddepcontrol.launch_dependents;")
+#define OB_PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
 #endif
 
 cudaStream_t stream();          // the stream work is currently issued on (the library's main stream unless forked)

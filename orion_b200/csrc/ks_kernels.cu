@@ -93,13 +93,13 @@ template <bool CENTERED, int NS, int VEC, int MM>
 __global__ void __launch_bounds__(BC_TPB)
 baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                       const ModConst* __restrict__ mc) {
-    OB_PDL_SYNC();
+    OB_PDL_LAUNCH();                                    // constants staged below are host-built: read before the wait
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const BcDev d = descs[blockIdx.y];
     const int ns = d.ns, nd = d.nd;
     const int chunk = (nd + gridDim.z - 1) / gridDim.z;
     const int t0 = blockIdx.z * chunk, ndc = min(nd, t0 + chunk) - t0;          // this CTA's destinations [t0, t0+ndc)
-    if (ndc <= 0) return;
+    if (ndc <= 0) { OB_PDL_WAIT(); return; }
     u64* s_mat = (u64*)smem_raw;                       // [ns][chunk]
     u64* s_neg = s_mat + ns * chunk;                   // [chunk][ns+1]
     double* s_matd = (double*)(s_neg + chunk * (ns + 1)); // [ns][chunk]
@@ -134,6 +134,7 @@ baseconv_batch_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, 
         s_sq[i] = m.q; s_sqd[i] = m.qd; s_inv[i] = d.inv[i]; s_sh[i] = CENTERED ? d.half_src[i] : 0;
     }
     __syncthreads();
+    OB_PDL_WAIT();
     const int x = (blockIdx.x * BC_TPB + threadIdx.x) * VEC;
     u64 y[VEC][NS];
     double yd[VEC][NS];
@@ -262,13 +263,13 @@ template <int RT, bool CENTERED>
 __global__ void __launch_bounds__(TC_TPB)
 baseconv_tc_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, const BcDev* __restrict__ descs,
                    const ModConst* __restrict__ mc) {
-    OB_PDL_SYNC();
+    OB_PDL_LAUNCH();                                    // the tables staged below are host-built: read before the wait
     extern __shared__ __align__(16) unsigned char tc_smem[];
     const BcDev d = descs[blockIdx.y];
     const int ns = d.ns, nd = d.nd;
     const int nblk = (nd + 3) >> 2, bchunk = (nblk + gridDim.z - 1) / gridDim.z;
     const int blk0 = blockIdx.z * bchunk, blk1 = min(nblk, blk0 + bchunk);
-    if (blk0 >= blk1) return;
+    if (blk0 >= blk1) { OB_PDL_WAIT(); return; }
     const int nb = blk1 - blk0;
     uint2* s_frag = (uint2*)tc_smem;
     TcDst* s_dst = (TcDst*)(s_frag + (size_t)bchunk * 256);
@@ -305,6 +306,7 @@ baseconv_tc_kernel(const u64* __restrict__ in, u64* __restrict__ out, int N, con
                 if (CENTERED) sh[h] = d.half_src[i];
             }
         }
+        OB_PDL_WAIT();                                  // `in` is the predecessor's output
 #pragma unroll
         for (int r = 0; r < RT; ++r) {
             double quo[2][2];

@@ -424,20 +424,25 @@ __global__ void __launch_bounds__(1 << (LOG_E - log_ept(STRIDED, FWD)))
 ntt_pass(const u64* in, u64* out, const LimbDesc* __restrict__ limbs,
          const ModConst* __restrict__ mc, const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all,
          const ulonglong2* __restrict__ ninv_all, int logN) {
-    OB_PDL_SYNC();
+    OB_PDL_LAUNCH();
     __shared__ __align__(16) u64 sm[(1 << LOG_E) + (1 << (LOG_E - 3))];         // padded layout, see pad()
-    const LimbDesc ld = limbs[blockIdx.y];
+    const LimbDesc ld = limbs[blockIdx.y];                                       // host-built tables: read before the wait
     const size_t N = (size_t)1 << logN;
     const ModConst& m = mc[ld.mod];
     const u64* src = in + (size_t)ld.in_off * N;
     u64* dst = out + (size_t)ld.out_off * N;
     const ulonglong2 ni = ninv_all[ld.mod];
     // aux bit 0 (forward first pass only): the limb already holds the FP64 policy's lazy values (kernels.h bc_raw_out)
-    if (m.bits <= F64_MAX_BITS)
-        ntt_body<ArithF64, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithF64(m), sm, src, dst, twd_all + (size_t)ld.mod * N, ni, logN,
+    if (m.bits <= F64_MAX_BITS) {
+        const ArithF64 ar(m);
+        OB_PDL_WAIT();
+        ntt_body<ArithF64, LOG_E, NBITS, STRIDED, FWD, FINAL>(ar, sm, src, dst, twd_all + (size_t)ld.mod * N, ni, logN,
                                                               nullptr, FWD && !FINAL && (ld.aux & 1));
-    else
-        ntt_body<ArithInt, LOG_E, NBITS, STRIDED, FWD, FINAL>(ArithInt(m), sm, src, dst, tw_all + (size_t)ld.mod * N, ni, logN);
+    } else {
+        const ArithInt ar(m);
+        OB_PDL_WAIT();
+        ntt_body<ArithInt, LOG_E, NBITS, STRIDED, FWD, FINAL>(ar, sm, src, dst, tw_all + (size_t)ld.mod * N, ni, logN);
+    }
 }
 
 // Fused second NTT pass + key-switch inner product (evaluator.cu step 3b + 4).  A CTA owns 1024 consecutive coefficients
@@ -599,11 +604,13 @@ ntt2_submul_kernel(const u64* __restrict__ a, int a_stride, const u64* __restric
                    const u64* __restrict__ addend, int addend_stride, int addend_polys, int addend_period, int addend_zstride,
                    u64* __restrict__ out, int out_stride, const ulonglong2* __restrict__ mulc, const ModConst* __restrict__ mc,
                    const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN) {
-    OB_PDL_SYNC();
+    OB_PDL_LAUNCH();
     __shared__ __align__(16) u64 sm[(1 << LOG_E_CONTIG) + (1 << (LOG_E_CONTIG - 3))];
     const int i = blockIdx.y, p = blockIdx.z;
     const size_t N = (size_t)1 << logN;
     const ModConst& m = mc[i];
+    const ulonglong2 mw = mulc[i];
+    const u64 mq = m.q;
     // polynomial p = z*period + c receives addend polynomial c of group z when c < addend_polys
     const int pz = p / addend_period, pc = p - pz * addend_period;
     const u64* ad = (addend != nullptr && pc < addend_polys)
@@ -611,10 +618,15 @@ ntt2_submul_kernel(const u64* __restrict__ a, int a_stride, const u64* __restric
     const u64* ap = a + ((size_t)p * a_stride + i) * N;
     const u64* bp = b + ((size_t)p * nl + i) * N;
     u64* op = out + ((size_t)p * out_stride + i) * N;
-    if (m.bits <= F64_MAX_BITS)
-        ntt2_submul_body<ArithF64>(ArithF64(m), sm, ap, bp, ad, op, twd_all + (size_t)i * N, mulc[i], m.q, logN);
-    else
-        ntt2_submul_body<ArithInt>(ArithInt(m), sm, ap, bp, ad, op, tw_all + (size_t)i * N, mulc[i], m.q, logN);
+    if (m.bits <= F64_MAX_BITS) {
+        const ArithF64 ar(m);
+        OB_PDL_WAIT();
+        ntt2_submul_body<ArithF64>(ar, sm, ap, bp, ad, op, twd_all + (size_t)i * N, mw, mq, logN);
+    } else {
+        const ArithInt ar(m);
+        OB_PDL_WAIT();
+        ntt2_submul_body<ArithInt>(ar, sm, ap, bp, ad, op, tw_all + (size_t)i * N, mw, mq, logN);
+    }
 }
 
 // ---- base conversion fused into the transforms either side of it (key switch: ModUp and ModDown) -------------------------
