@@ -37,6 +37,11 @@ inline void alg_bytes(double b) { g_alg_bytes += b; }
 // completed and flushed.  Overlaps the tail wave of large kernels with the head of the next; policy in context.cu
 // (pdl_enabled: on for logN >= 15, ORION_B200_PDL=0/1 overrides).
 bool pdl_enabled();
+// Launch sequences whose descriptors are written by a KERNEL (csrc/noalloc.cu) must not be programmatic dependent launches: the
+// consumers read their descriptors before griddepcontrol.wait (OB_PDL_LAUNCH / OB_PDL_WAIT below).  While a PdlSuppress is alive
+// every launch is an ordinary, fully ordered one.
+extern int g_pdl_suppress;
+struct PdlSuppress { PdlSuppress() { ++g_pdl_suppress; } ~PdlSuppress() { --g_pdl_suppress; } };
 // Kernel probe: while enabled, the launcher of the key switch's dominant kernel brackets it with CUDA events on its own
 // stream (bench.py's roofline.achieved); probe_read sums the elapsed times and clears the list.
 // Slots name the stages of a key switch (PROBE_* below); slot 0 is the dominant kernel.  Events between launches keep the

@@ -61,9 +61,11 @@ EvRef record_event(cudaStream_t s) {
 // lanes it cost 9 % there: early-resident dependents took SM slots from the side streams' kernels; with eight lanes the
 // shorter kernel-to-kernel gap of every chain wins).  Default: on for every ring; ORION_B200_PDL=0/1 overrides.
 static bool g_pdl_auto = true;
+int g_pdl_suppress = 0;
 bool pdl_enabled() {
     static int forced = -2;
     if (forced == -2) { const char* s = std::getenv("ORION_B200_PDL"); forced = s ? (std::atoi(s) != 0) : -1; }
+    if (g_pdl_suppress) return false;
     return forced >= 0 ? forced == 1 : g_pdl_auto;
 }
 namespace {

@@ -94,6 +94,9 @@ int B200_RescaleDevNoAlloc(void* h, int level, const void* in, void* out, int po
     u64* last = (u64*)s;                                   // [polys][N]
     u64* tmp = last + (size_t)polys * N;                   // [polys][level][N]
     LimbDesc* d = (LimbDesc*)(s + NOALLOC_MAX_WORDS);
+    // the descriptors are written by a kernel, and the transforms read their descriptors BEFORE griddepcontrol.wait (they are
+    // host-built tables everywhere else): this sequence runs as ordinary, fully ordered launches
+    PdlSuppress no_pdl;
     OB_LAUNCH(noalloc_fill_desc_kernel, 1, 128, 0, stream(), d, level, polys, level + 1);
     NttPlan inv; inv.first = d; inv.second = d + polys; inv.n = polys;
     NttPlan fwd; fwd.first = d + 2 * polys; fwd.second = d + 2 * polys; fwd.n = polys * level;
