@@ -409,6 +409,8 @@ def main():
         resnet = run_resnet(lib, rank, world, dist if world > 1 else None, torch, peak)
         if world > 1 and resnet is not None:
             resnet["strong_scaling"] = run_resnet_sharded(lib, rank, world, dist, torch, meta_group)
+        if world == 1 and resnet is not None and not args.no_extras:
+            resnet["lockstep"] = run_resnet_lockstep(lib, rank)
         lola = run_lola(lib, rank, world, dist if world > 1 else None, torch)
         if os.environ.get("ORION_B200_BENCH_RESNET16", "1") != "0":                   # last: it needs the whole GPU's memory
             resnet16 = run_resnet16(lib, rank, world, dist if world > 1 else None, torch, peak)
@@ -558,6 +560,29 @@ def run_resnet(lib, rank, world, dist, torch, peak=None, reps=3):
                         "(diagonals, biases, sign polynomials) recorded from the unmodified reference",
                 "e2e": "includes encode+encrypt (H2D) of the image and decrypt+decode (D2H) of the logits"})
     return res
+
+
+def run_resnet_lockstep(lib, rank, k=4, reps=2):
+    """K images per GPU in lockstep over ONE scheme (orion_b200.replay.BatchReplayer): call i of image 0, call i of image 1, ... --
+    the images' ciphertexts are independent, so the library's dataflow lanes overlap their small-ring launches.  images/s per GPU."""
+    from orion_b200.bindings import B200Library
+    from orion_b200.replay import BatchReplayer, Trace
+    gold = os.path.join(ROOT, "tests", "golden")
+    t = Trace(os.path.join(gold, "trace_resnet20.json"), os.path.join(gold, "trace_resnet20.npz"))
+    B = B200Library()
+    B.B200_SetSeed(42 + rank)
+    r = BatchReplayer(B, t, k)
+    r.setup(); lib.B200_Sync()
+    outs = r.infer(); lib.B200_Sync()
+    best = float("inf")
+    for _ in range(reps):
+        lib.B200_Sync(); lib.B200_TimerStart()
+        outs = r.infer()
+        best = min(best, lib.B200_TimerStopMs() / 1e3)
+    clear = np.array(t.meta["clear_output"], dtype=np.float64)
+    err = max(float(np.max(np.abs(np.asarray(o, dtype=np.float64)[: clear.size] - clear))) for o in outs)
+    B.DeleteScheme()
+    return {"images_in_flight": k, "s_per_batch": best, "images_per_s_per_gpu": k / best, "max_abs_err": err}
 
 
 def run_resnet_sharded(lib, rank, world, dist, torch, meta_group, name="resnet20", reps=3):

@@ -400,12 +400,25 @@ inner_product_kernel(const u64* __restrict__ c1, const u64* __restrict__ digits,
     const int own = t < L ? t / K : -1;
     const int xs = GATHER ? (int)__ldg(&gather[x]) : x;
     u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
-    for (int j = 0; j < beta; ++j) {
-        const u64 d = (j == own) ? c1[(size_t)t * N + xs] : digits[((size_t)j * W + t) * N + xs];
-        const u64 k0 = evk[(((size_t)j * 2 + 0) * nmod + ci) * N + x];
-        const u64 k1 = evk[(((size_t)j * 2 + 1) * nmod + ci) * N + x];
-        mac128(h0, l0, d, k0, m.q);
-        mac128(h1, l1, d, k1, m.q);
+    if ((m.q >> 32) == 0) {                          // limb below 2^32: word-sized products, folded every 2^(64 - 2 bits) terms
+        const int fold = 1 << min(30, 64 - 2 * m.bits);
+        u64 s0 = 0, s1 = 0;
+        int cnt = 0;
+        for (int j = 0; j < beta; ++j) {
+            const u64 d = (j == own) ? c1[(size_t)t * N + xs] : digits[((size_t)j * W + t) * N + xs];
+            s0 += (u64)(uint32_t)d * (uint32_t)evk[(((size_t)j * 2 + 0) * nmod + ci) * N + x];
+            s1 += (u64)(uint32_t)d * (uint32_t)evk[(((size_t)j * 2 + 1) * nmod + ci) * N + x];
+            if (++cnt == fold) { l0 += s0; h0 += (l0 < s0); l1 += s1; h1 += (l1 < s1); s0 = s1 = 0; cnt = 0; }
+        }
+        l0 += s0; h0 += (l0 < s0); l1 += s1; h1 += (l1 < s1);
+    } else {
+        for (int j = 0; j < beta; ++j) {
+            const u64 d = (j == own) ? c1[(size_t)t * N + xs] : digits[((size_t)j * W + t) * N + xs];
+            const u64 k0 = evk[(((size_t)j * 2 + 0) * nmod + ci) * N + x];
+            const u64 k1 = evk[(((size_t)j * 2 + 1) * nmod + ci) * N + x];
+            mac128(h0, l0, d, k0, m.q);
+            mac128(h1, l1, d, k1, m.q);
+        }
     }
     u64 r0 = mont_redc(h0, l0, m.q, m.qinv_neg), r1 = mont_redc(h1, l1, m.q, m.qinv_neg);
     const size_t o0 = (size_t)t * N + x, o1 = ((size_t)W + t) * N + x;
@@ -436,13 +449,36 @@ inner_product_multi_kernel(const u64* __restrict__ c1, size_t c1_zstride, const 
     const u64* __restrict__ c1z = c1 + (size_t)z * c1_zstride;
     const u64* __restrict__ dz = digits + (size_t)z * dig_zstride;
     u64 h0a = 0, l0a = 0, h1a = 0, l1a = 0, h0b = 0, l0b = 0, h1b = 0, l1b = 0;
+    if ((mm.q >> 32) == 0) {
+        // limb below 2^32 (30-bit scale primes): each product fits a word and 2^(64 - 2 bits) of them are summed with one
+        // IMAD.WIDE each before the partial sum is folded into the 128-bit accumulator (same exact sum, same REDC)
+        const int fold = 1 << min(30, 64 - 2 * mm.bits);
+        u64 s0a = 0, s1a = 0, s0b = 0, s1b = 0;
+        int cnt = 0;
 #pragma unroll 2
-    for (int j = 0; j < beta; ++j) {
-        const ulonglong2 d = *(const ulonglong2*)((j == own) ? c1z + (size_t)t * N + x : dz + ((size_t)j * W + t) * N + x);
-        const ulonglong2 k0 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 0) * nmod + ci) * N + x);
-        const ulonglong2 k1 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 1) * nmod + ci) * N + x);
-        mac128(h0a, l0a, d.x, k0.x, mm.q); mac128(h0b, l0b, d.y, k0.y, mm.q);
-        mac128(h1a, l1a, d.x, k1.x, mm.q); mac128(h1b, l1b, d.y, k1.y, mm.q);
+        for (int j = 0; j < beta; ++j) {
+            const ulonglong2 d = *(const ulonglong2*)((j == own) ? c1z + (size_t)t * N + x : dz + ((size_t)j * W + t) * N + x);
+            const ulonglong2 k0 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 0) * nmod + ci) * N + x);
+            const ulonglong2 k1 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 1) * nmod + ci) * N + x);
+            s0a += (u64)(uint32_t)d.x * (uint32_t)k0.x; s0b += (u64)(uint32_t)d.y * (uint32_t)k0.y;
+            s1a += (u64)(uint32_t)d.x * (uint32_t)k1.x; s1b += (u64)(uint32_t)d.y * (uint32_t)k1.y;
+            if (++cnt == fold) {
+                l0a += s0a; h0a += (l0a < s0a); l0b += s0b; h0b += (l0b < s0b);
+                l1a += s1a; h1a += (l1a < s1a); l1b += s1b; h1b += (l1b < s1b);
+                s0a = s1a = s0b = s1b = 0; cnt = 0;
+            }
+        }
+        l0a += s0a; h0a += (l0a < s0a); l0b += s0b; h0b += (l0b < s0b);
+        l1a += s1a; h1a += (l1a < s1a); l1b += s1b; h1b += (l1b < s1b);
+    } else {
+#pragma unroll 2
+        for (int j = 0; j < beta; ++j) {
+            const ulonglong2 d = *(const ulonglong2*)((j == own) ? c1z + (size_t)t * N + x : dz + ((size_t)j * W + t) * N + x);
+            const ulonglong2 k0 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 0) * nmod + ci) * N + x);
+            const ulonglong2 k1 = *(const ulonglong2*)(evk + (((size_t)j * 2 + 1) * nmod + ci) * N + x);
+            mac128(h0a, l0a, d.x, k0.x, mm.q); mac128(h0b, l0b, d.y, k0.y, mm.q);
+            mac128(h1a, l1a, d.x, k1.x, mm.q); mac128(h1b, l1b, d.y, k1.y, mm.q);
+        }
     }
     ulonglong2 r0 = make_ulonglong2(mont_redc(h0a, l0a, mm.q, mm.qinv_neg), mont_redc(h0b, l0b, mm.q, mm.qinv_neg));
     ulonglong2 r1 = make_ulonglong2(mont_redc(h1a, l1a, mm.q, mm.qinv_neg), mont_redc(h1b, l1b, mm.q, mm.qinv_neg));

@@ -25,27 +25,53 @@ constexpr int TPB = 256;
 // blockIdx.z = giant step z (all giant steps of a transform in one launch)
 constexpr int LTM_MAX = 64;
 struct LtMacMulti { const int2* pairs[LTM_MAX]; int np[LTM_MAX]; };
+// Two adjacent coefficients per thread (128-bit streams).  Limbs below 2^32 (the 30-bit scale primes of the shipped
+// ResNet-20 / LoLA chains: 33 of 35 limbs): every product fits a word, 2^(64 - 2 bits) of them are summed with one IMAD.WIDE
+// each before the partial sum is folded into the 128-bit accumulator; larger limbs keep the 128-bit multiply-accumulate
+// with its conditional high-word reduction.  Same words either way (one REDC of the exact sum).
 __global__ void __launch_bounds__(TPB)
 lt_mac_kernel(const u64* __restrict__ diags, const u64* __restrict__ rots, const LtMacMulti mm, u64* __restrict__ acc_all,
               int N, int L, int W, int L_lt, int W_lt, int nQ, const ModConst* __restrict__ mc) {
     OB_PDL_SYNC();
-    const int t = blockIdx.y, x = blockIdx.x * TPB + threadIdx.x, z = blockIdx.z;
+    const int t = blockIdx.y, x = (blockIdx.x * TPB + threadIdx.x) * 2, z = blockIdx.z;
     const int ci = t < L ? t : nQ + (t - L);
     const int td = t < L ? t : L_lt + (t - L);
     const ModConst m = mc[ci];
     const int2* __restrict__ pairs = mm.pairs[z];
     const int npairs = mm.np[z];
     u64* acc = acc_all + (size_t)z * 2 * W * N;
-    u64 h0 = 0, l0 = 0, h1 = 0, l1 = 0;
-    for (int k = 0; k < npairs; ++k) {
-        const int2 pr = __ldg(&pairs[k]);
-        const u64 d = diags[((size_t)pr.x * W_lt + td) * N + x];
-        const u64* r = rots + (size_t)pr.y * 2 * W * N;
-        mac128(h0, l0, d, r[(size_t)t * N + x], m.q);
-        mac128(h1, l1, d, r[((size_t)W + t) * N + x], m.q);
+    u64 h0a = 0, l0a = 0, h1a = 0, l1a = 0, h0b = 0, l0b = 0, h1b = 0, l1b = 0;
+    if ((m.q >> 32) == 0) {
+        const int fold = 1 << min(30, 64 - 2 * m.bits);
+        u64 s0a = 0, s1a = 0, s0b = 0, s1b = 0;
+        int cnt = 0;
+        for (int k = 0; k < npairs; ++k) {
+            const int2 pr = __ldg(&pairs[k]);
+            const ulonglong2 d = *(const ulonglong2*)(diags + ((size_t)pr.x * W_lt + td) * N + x);
+            const u64* r = rots + (size_t)pr.y * 2 * W * N;
+            const ulonglong2 r0 = *(const ulonglong2*)(r + (size_t)t * N + x), r1 = *(const ulonglong2*)(r + ((size_t)W + t) * N + x);
+            s0a += (u64)(uint32_t)d.x * (uint32_t)r0.x; s0b += (u64)(uint32_t)d.y * (uint32_t)r0.y;
+            s1a += (u64)(uint32_t)d.x * (uint32_t)r1.x; s1b += (u64)(uint32_t)d.y * (uint32_t)r1.y;
+            if (++cnt == fold) {
+                l0a += s0a; h0a += (l0a < s0a); l0b += s0b; h0b += (l0b < s0b);
+                l1a += s1a; h1a += (l1a < s1a); l1b += s1b; h1b += (l1b < s1b);
+                s0a = s1a = s0b = s1b = 0; cnt = 0;
+            }
+        }
+        l0a += s0a; h0a += (l0a < s0a); l0b += s0b; h0b += (l0b < s0b);
+        l1a += s1a; h1a += (l1a < s1a); l1b += s1b; h1b += (l1b < s1b);
+    } else {
+        for (int k = 0; k < npairs; ++k) {
+            const int2 pr = __ldg(&pairs[k]);
+            const ulonglong2 d = *(const ulonglong2*)(diags + ((size_t)pr.x * W_lt + td) * N + x);
+            const u64* r = rots + (size_t)pr.y * 2 * W * N;
+            const ulonglong2 r0 = *(const ulonglong2*)(r + (size_t)t * N + x), r1 = *(const ulonglong2*)(r + ((size_t)W + t) * N + x);
+            mac128(h0a, l0a, d.x, r0.x, m.q); mac128(h0b, l0b, d.y, r0.y, m.q);
+            mac128(h1a, l1a, d.x, r1.x, m.q); mac128(h1b, l1b, d.y, r1.y, m.q);
+        }
     }
-    acc[(size_t)t * N + x] = mont_redc(h0, l0, m.q, m.qinv_neg);
-    acc[((size_t)W + t) * N + x] = mont_redc(h1, l1, m.q, m.qinv_neg);
+    *(ulonglong2*)(acc + (size_t)t * N + x) = make_ulonglong2(mont_redc(h0a, l0a, m.q, m.qinv_neg), mont_redc(h0b, l0b, m.q, m.qinv_neg));
+    *(ulonglong2*)(acc + ((size_t)W + t) * N + x) = make_ulonglong2(mont_redc(h1a, l1a, m.q, m.qinv_neg), mont_redc(h1b, l1b, m.q, m.qinv_neg));
 }
 
 // out[p][t][x] = t < L ? (P mod q_t) * c[p][t][x] : 0        (lift of a Q-basis ciphertext to "P * ct" in QP)
@@ -216,7 +242,7 @@ std::unique_ptr<Ciphertext> lt_apply(Scheme& s, const LinearTransform& lt, const
         DevBuf accs((size_t)n * PW * 8);
         LtMacMulti mm{};
         for (int z = 0; z < n; ++z) { mm.pairs[z] = gp[zc + z]->as<int2>(); mm.np[z] = gn[zc + z]; }
-        OB_LAUNCH(lt_mac_kernel, dim3(N / TPB, W, n), TPB, 0, stream(), lt.diags.u(), rots.u(), mm, accs.u(), N, L, W,
+        OB_LAUNCH(lt_mac_kernel, dim3(N / (2 * TPB), W, n), TPB, 0, stream(), lt.diags.u(), rots.u(), mm, accs.u(), N, L, W,
                   lt.level + 1, lt.W, c.nQ, c.dmc());
         const int zr = (zc == 0) ? z_first : 0;                 // first rotated step of this chunk
         const int nr = n - zr;
