@@ -312,12 +312,14 @@ def test_bootstrap_precision_at_the_resnet20_parameter_set(orc, b200lib, num_slo
         B.DeleteScheme()
 
 
-@pytest.mark.parametrize("num_slots", [2048, 256])
-def test_bootstrap_words_equal_the_oracles(orc, b200lib, num_slots):
+@pytest.mark.parametrize("num_slots,boot_p", [(2048, 4), (256, 4), (2048, 8)])
+def test_bootstrap_words_equal_the_oracles(orc, b200lib, num_slots, boot_p):
     """a16, word for word: Bootstrap() on the GPU (ScaleUp, ModRaise, SubSum, 4 CoeffsToSlots transforms, EvalMod on both
     halves -- degree-63 Chebyshev + double-angle steps --, 3 SlotsToCoeffs transforms; ~30 rotations keys, ~100 key switches)
     returns the ciphertext oracle/bootstrap.py computes on the CPU from the same input ciphertext and seed.  Full and sparse
-    slot counts (the sparse one adds the SubSum rotations and the shim's post-factor)."""
+    slot counts (the sparse one adds the SubSum rotations and the shim's post-factor); with 8 bootstrapping special primes the
+    ModUp / ModDown conversions have 8-source digits, i.e. they run on the INT8 tensor-core kernel (csrc/ks_kernels.cu
+    baseconv_tc_kernel), plain and centred -- the shape of the shipped ResNet-20 configuration (boot LogP 8 x 61)."""
     from oracle.bootstrap import OBootstrapper
     from oracle.scheme import OScheme
     from orion_b200.bindings import B200Library
@@ -340,8 +342,8 @@ def test_bootstrap_words_equal_the_oracles(orc, b200lib, num_slots):
         ct = B.Encrypt(B.B200_EncodeF64(xin, slots, 1, float(1 << logscale)))
         oct_ = O.encrypt(O.encode(xin, 1, 2.0 ** logscale))
         assert np.array_equal(export_ct(B, O, ct), oct_.data)
-        B.NewBootstrapper([61, 61, 61, 61], num_slots)
-        ob = OBootstrapper(O, [61, 61, 61, 61], num_slots)
+        B.NewBootstrapper([61] * boot_p, num_slots)
+        ob = OBootstrapper(O, [61] * boot_p, num_slots)
         got = export_ct(B, O, B.Bootstrap(ct, num_slots))
         want = ob.bootstrap(oct_)
         assert got.shape == want.data.shape
