@@ -499,7 +499,7 @@ def check_against_oracle(lib, raw, w, last_step):
     return {"equal": bool(np.array_equal(out, ref)), "what": how + ": B200_KeySwitchBatchDev (n=%d, +c0) vs oracle.Ctx.keyswitch, %d words" % (GROUP, out.size)}
 
 
-def run_trace_timed(name, lib, rank, world, dist, torch, reps=3, peak=None, warm=2):
+def run_trace_timed(name, lib, rank, world, dist, torch, reps=3, peak=None, warm=4):
     """Replay the reference's recorded call trace `name`, one image per rank; returns timing fields or None.
     The timed region of an inference includes encode + encrypt of the image (H2D) and decrypt + decode of the logits (D2H)."""
     from orion_b200.bindings import B200Library
@@ -515,7 +515,7 @@ def run_trace_timed(name, lib, rank, world, dist, torch, reps=3, peak=None, warm
     t0 = time.perf_counter(); r.setup(); lib.B200_Sync(); setup_s = time.perf_counter() - t0
     out = None
     for _ in range(warm):
-        out = r.infer(); lib.B200_Sync()                         # warm-up (plans, key caches, pool growth, side streams)
+        out = r.infer(); lib.B200_Sync()                         # warm-up (plans, key caches, pool growth, side streams, graph captures)
     l0 = lib.B200_LaunchCount()
     a0 = lib.B200_AlgorithmicBytes()
     times = []

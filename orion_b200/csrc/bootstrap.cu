@@ -20,8 +20,10 @@
 #include "bootstrap.h"
 #include "lintrans.h"
 #include "polyeval.h"
+#include "graphs.h"
 #include <algorithm>
 #include <cmath>
+#include <ctime>
 #include <complex>
 
 namespace ob {
@@ -190,7 +192,8 @@ std::vector<double> cheb_interp(int deg, double K1, int r) {
 }
 }  // namespace
 
-void boot_reset() { if (!g_boot.empty()) cudaStreamSynchronize(stream()); g_boot.clear(); }
+void boot_graphs_reset();
+void boot_reset() { if (!g_boot.empty()) cudaStreamSynchronize(stream()); boot_graphs_reset(); g_boot.clear(); graphs_invalidate(); }
 
 // memory pressure (common.h): encoded DFT factor sets are re-encodable from the host factors -- parked sets first (LRU), then
 // the current set of every bootstrapper that is not inside boot_apply
@@ -342,6 +345,7 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
             auto& e = b.encoded[b.built_for_scale];
             e.cts = std::move(b.cts); e.stc = std::move(b.stc); e.last_use = ++b.use_clock;
             while (b.encoded.size() > 6) {
+                capture_abort(); graphs_invalidate();             // a captured bootstrap may point at the set that goes
                 auto old = b.encoded.begin();
                 for (auto i = b.encoded.begin(); i != b.encoded.end(); ++i) if (i->second.last_use < old->second.last_use) old = i;
                 OB_CUDA(cudaDeviceSynchronize());                 // bootstraps on other lanes may still read these factors
@@ -466,6 +470,21 @@ std::unique_ptr<Ciphertext> boot_apply(Scheme& s, const Ciphertext& in, int num_
     auto out = s.new_ct(out_level, 1, s.default_scale, in.log_slots);
     OB_CUDA(cudaMemcpyAsync(out->data.p, ct->data.p, out->data.bytes, cudaMemcpyDeviceToDevice, stream()));
     return out;
+}
+
+// ---- Bootstrap as a captured CUDA graph (graphs.h) ----------------------------------------------------------------------------
+namespace {
+typedef std::tuple<int, int, long double, int> BootGraphKey;       // slot count, input level, input scale, input slots
+std::map<BootGraphKey, UnaryGraphSet>& boot_graphs() { static auto* m = new std::map<BootGraphKey, UnaryGraphSet>(); return *m; }
+}  // namespace
+void boot_graphs_reset() { cudaDeviceSynchronize(); boot_graphs().clear(); }
+
+std::unique_ptr<Ciphertext> boot_apply_graphed(Scheme& s, const Ciphertext& in, int num_slots) {
+    if (!graphs_enabled(s.ctx->logN) || dump_dir() || std::getenv("ORION_B200_BOOT_DEBUG")) return boot_apply(s, in, num_slots);
+    UnaryGraphSet& set = boot_graphs()[BootGraphKey(num_slots, in.level, (long double)in.scale, in.log_slots)];
+    // scratch of one bootstrap of the ResNet-20 chain at N = 8192: just under 2 GB with the per-stream reuse of the arena
+    return run_unary_graphed(s, set, in, std::max<size_t>((size_t)1 << 30, (size_t)s.N << 18), "bootstrap",
+                             [&](const Ciphertext& x) { return boot_apply(s, x, num_slots); });
 }
 
 }  // namespace ob

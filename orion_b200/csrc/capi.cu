@@ -539,6 +539,6 @@ int GetPolyDepth(int poly) { return poly_depth(poly_get(poly)); }
 
 // ---------------------------------------------------------------- bootstrapping (LG/bootstrapper.go:19-93)
 void NewBootstrapper(int* logPs, int n, int numSlots) { boot_new(S(), std::vector<int>(logPs, logPs + n), numSlots); }
-int Bootstrap(int ct, int numSlots) { return op_new(true, {&CT(ct).trk}, [&] { return boot_apply(S(), CT(ct), numSlots); }); }
+int Bootstrap(int ct, int numSlots) { return op_new(true, {&CT(ct).trk}, [&] { return boot_apply_graphed(S(), CT(ct), numSlots); }); }
 void DeleteBootstrappers(void) { settle_all(); boot_reset(); }
 }  // extern "C"

@@ -23,8 +23,13 @@ namespace ob {
 }
 #define OB_FATAL(msg) ::ob::fatal(__FILE__, __LINE__, (msg))
 #define OB_CHECK(cond, msg) do { if (!(cond)) OB_FATAL(std::string("check failed: " #cond " -- ") + (msg)); } while (0)
-#define OB_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) \
-    OB_FATAL(std::string("CUDA error: ") + cudaGetErrorString(e__) + " in " #call); } while (0)
+// While a launch sequence is being captured into a CUDA graph (g_capturing), a failing call does not abort: it marks the capture
+// failed and the sequence carries on (nothing executes during capture); the capturer then discards the graph and runs eagerly.
+extern int g_capturing;
+extern bool g_capture_failed;
+#define OB_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { \
+    if (::ob::g_capturing) { ::ob::g_capture_failed = true; cudaGetLastError(); } \
+    else OB_FATAL(std::string("CUDA error: ") + cudaGetErrorString(e__) + " in " #call); } } while (0)
 
 // launch counter: every kernel of this library goes through OB_LAUNCH so bench.py can report gpu_launches
 extern unsigned long long g_launches;
@@ -151,18 +156,48 @@ void unregister_reclaimer(int id);
 unsigned long long use_tick();                              // monotonic use clock (LRU stamps)
 unsigned long long pin_floor();                             // stamps >= this belong to the operation in progress
 struct OpPin { OpPin(); ~OpPin(); OpPin(const OpPin&) = delete; OpPin& operator=(const OpPin&) = delete; };
+// Captured CUDA graphs (bootstrap.cu, polyeval.cu) bake device addresses of shared state: whoever frees or rebuilds such state
+// (evicted Galois keys, re-encoded / dropped bootstrap factor sets, deleted polynomials or schemes) bumps the epoch, and a
+// graph captured under an older epoch is discarded and captured again.
+extern unsigned long long g_graph_epoch;
+inline void graphs_invalidate() { ++g_graph_epoch; }
+bool graphs_enabled(int logN);                             // ORION_B200_GRAPHS=0/1; default: on for logN <= 14
 unsigned long long reclaimed_bytes();                       // diagnostics: total bytes given back under pressure
-size_t device_bytes(bool peak);                             // bytes held through DevBuf now / at their high-water mark
+size_t device_bytes(bool peak);
+void device_bytes_mark();                                   // start measuring the scratch need of a call ...
+size_t device_bytes_since_mark();                           // ... its high-water mark above the level at the mark                             // bytes held through DevBuf now / at their high-water mark
 
+// While a sequence is captured into a CUDA graph, its scratch buffers come from a CaptureArena instead of the pool: a persistent
+// device range owned by the graph, carved by a host-side allocator with one free list per stream (a block freed on a stream is
+// reused only by later allocations on that stream -- the ordering contract of cudaFreeAsync / cudaMallocAsync), so the graph holds
+// kernels and copies only (memory nodes made a 1 700-node bootstrap graph cost 10 ms per launch on the host).
+struct CaptureArena {
+    char* base = nullptr;
+    size_t cap = 0, top = 0;
+    bool overflow = false;
+    std::map<cudaStream_t, std::multimap<size_t, size_t>> free_;      // stream -> (size -> offset)
+    void* alloc(size_t n, cudaStream_t s);
+    void free(void* p, size_t n, cudaStream_t s);
+};
+extern CaptureArena* g_arena;                                 // non-null while capturing
+// capture_begin / capture_end bracket a launch sequence on `origin`; capture_end returns the graph, or nullptr when anything in
+// between failed.  capture_abort() is called wherever PERSISTENT device state is created lazily (tables, plans, keys, encoded
+// factors): such state must be built for real, from the pool, so the capture is ended on the spot (the rest of the sequence then
+// runs eagerly on scratch addresses -- garbage in, garbage out, confined to the arena) and the capturer repeats the whole call
+// eagerly.  Steady-state sequences never get there: the capturer runs a key eagerly once before it captures it.
+bool capture_begin(cudaStream_t origin, CaptureArena* arena);
+cudaGraph_t capture_end();
+void capture_abort();
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
+    bool arena = false;                                        // carved from a CaptureArena: never goes back to the pool
     DevBuf() {}
     explicit DevBuf(size_t n) { alloc(n); }
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
-    DevBuf& operator=(DevBuf&& o) noexcept { if (this != &o) { release(); p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; } return *this; }
+    DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes), arena(o.arena) { o.p = nullptr; o.bytes = 0; o.arena = false; }
+    DevBuf& operator=(DevBuf&& o) noexcept { if (this != &o) { release(); p = o.p; bytes = o.bytes; arena = o.arena; o.p = nullptr; o.bytes = 0; o.arena = false; } return *this; }
     ~DevBuf() { release(); }
     void alloc(size_t n);
     void release();

@@ -220,6 +220,7 @@ int g_reclaimer_id = 0, g_pin_depth = 0;
 unsigned long long g_use_clock = 1, g_pin_floor = ~0ull, g_reclaimed = 0;
 bool g_reclaiming = false;
 size_t g_dev_bytes = 0, g_dev_peak = 0;                    // bytes currently held through DevBuf, and their high-water mark
+size_t g_dev_peak2 = 0, g_dev_mark = 0;                    // high-water mark since device_bytes_mark() (scratch need of one call)
 // ORION_B200_MEM_LIMIT_MB: treat DevBuf allocations beyond this total as out of memory (exercises the reclaim path on a small ring)
 size_t mem_limit() { static const size_t l = std::getenv("ORION_B200_MEM_LIMIT_MB") ? (size_t)std::atoll(std::getenv("ORION_B200_MEM_LIMIT_MB")) << 20 : 0; return l; }
 cudaError_t try_alloc(void** p, size_t n) {
@@ -234,13 +235,24 @@ void unregister_reclaimer(int id) { reclaimers().erase(id); }
 unsigned long long use_tick() { return ++g_use_clock; }
 unsigned long long pin_floor() { return g_pin_depth ? g_pin_floor : ~0ull; }
 unsigned long long reclaimed_bytes() { return g_reclaimed; }
+unsigned long long g_graph_epoch = 1;
+int g_capturing = 0;
+bool g_capture_failed = false;
+bool graphs_enabled(int logN) {
+    static const int forced = [] { const char* e = std::getenv("ORION_B200_GRAPHS"); return e ? (std::atoi(e) != 0 ? 1 : 0) : -1; }();
+    if (forced >= 0) return forced == 1;
+    return logN <= 14;
+}
 size_t device_bytes(bool peak) { return peak ? g_dev_peak : g_dev_bytes; }
+void device_bytes_mark() { g_dev_mark = g_dev_bytes; g_dev_peak2 = g_dev_bytes; }
+size_t device_bytes_since_mark() { return g_dev_peak2 - g_dev_mark; }
 OpPin::OpPin() { if (g_pin_depth++ == 0) g_pin_floor = ++g_use_clock; }
 OpPin::~OpPin() { --g_pin_depth; }
 
 // the pool is out of memory: device-wide synchronisation (frees queued on any lane complete, nothing in flight reads what is
 // about to be evicted), retry; then evict through the reclaimers, a few GB at a time, until the allocation fits
 static void* alloc_under_pressure(size_t n) {
+    capture_abort();
     void* p = nullptr;
     OB_CHECK(!g_reclaiming, "out of device memory while reclaiming");
     g_reclaiming = true;
@@ -252,6 +264,7 @@ static void* alloc_under_pressure(size_t n) {
         size_t freed = 0;
         for (auto& kv : reclaimers()) { if (freed >= want) break; freed += kv.second(want - freed); }
         g_reclaimed += freed;
+        if (freed) graphs_invalidate();
         if (verbose) std::fprintf(stderr, "[mem] allocation of %.2f GB failed: reclaimed %.2f GB (round %d)\n", n / 1073741824.0, freed / 1073741824.0, round);
         if (freed == 0) {
             // last resort: hand the pool's unused blocks back to the driver so that it can re-map them into one range
@@ -269,16 +282,66 @@ static void* alloc_under_pressure(size_t n) {
              std::to_string(tot >> 20) + " MiB, nothing left to reclaim)");
     return nullptr;
 }
+CaptureArena* g_arena = nullptr;
+static cudaStream_t g_capture_origin = nullptr;
+bool capture_begin(cudaStream_t origin, CaptureArena* arena) {
+    if (g_capturing) return false;
+    if (cudaStreamBeginCapture(origin, cudaStreamCaptureModeRelaxed) != cudaSuccess) { cudaGetLastError(); return false; }
+    g_capturing = 1; g_capture_failed = false; g_capture_origin = origin; g_arena = arena;
+    return true;
+}
+cudaGraph_t capture_end() {
+    if (!g_capturing) return nullptr;                          // aborted on the way
+    g_capturing = 0; g_arena = nullptr;
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(g_capture_origin, &graph);
+    if (e != cudaSuccess || g_capture_failed) { cudaGetLastError(); if (graph) cudaGraphDestroy(graph); return nullptr; }
+    return graph;
+}
+void capture_abort() {
+    if (!g_capturing) return;
+    g_capturing = 0; g_capture_failed = true; g_arena = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaStreamEndCapture(g_capture_origin, &graph);
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+}
+void* CaptureArena::alloc(size_t n, cudaStream_t s) {
+    n = (n + 255) & ~(size_t)255;
+    auto& fl = free_[s];
+    auto it = fl.lower_bound(n);
+    if (it != fl.end() && it->first <= n + (n >> 1)) {                // best fit, at most 50 % waste
+        const size_t off = it->second;
+        fl.erase(it);
+        return base + off;
+    }
+    if (top + n > cap) { overflow = true; return nullptr; }          // the capture is discarded (DevBuf::alloc falls back to the pool)
+    void* p = base + top;
+    top += n;
+    return p;
+}
+void CaptureArena::free(void* p, size_t n, cudaStream_t s) {
+    if (overflow) return;
+    n = (n + 255) & ~(size_t)255;
+    free_[s].emplace(n, (size_t)((char*)p - base));
+}
 void DevBuf::alloc(size_t n) {
     release();
     if (n == 0) return;
+    if (g_arena) {
+        void* q = g_arena->alloc(n, stream());
+        if (!g_arena->overflow) { p = q; bytes = n; arena = true; return; }
+        capture_abort();                                       // scratch does not fit: the capture is over, the rest runs from the pool
+    }
     OB_HP("cudaMallocAsync");
     const cudaError_t e = try_alloc(&p, n);
     if (e == cudaErrorMemoryAllocation) p = alloc_under_pressure(n);
     else OB_CUDA(e);
     bytes = n; g_dev_bytes += n; if (g_dev_bytes > g_dev_peak) g_dev_peak = g_dev_bytes;
+    if (g_dev_bytes > g_dev_peak2) g_dev_peak2 = g_dev_bytes;
 }
 void DevBuf::release() {
+    if (p && arena) { if (g_arena) g_arena->free(p, bytes, g_cur ? g_cur : g_stream); p = nullptr; bytes = 0; arena = false; return; }
     if (p) { OB_HP("cudaFreeAsync"); cudaFreeAsync(p, g_cur ? g_cur : g_stream); p = nullptr; g_dev_bytes -= bytes; bytes = 0; }
 }
 
@@ -413,6 +476,7 @@ static uint32_t bitrev_u32(uint32_t x, int bits) {
 
 template <class T>
 static void upload(DevBuf& d, const std::vector<T>& h) {
+    capture_abort();                                           // a table built lazily: for real, from the pool
     d.alloc(h.size() * sizeof(T));
     if (!h.empty()) {
         OB_CUDA(cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, stream()));

@@ -77,6 +77,7 @@ static bool use_fused_ip(const Context& c, int W, int n) {
 }
 
 const BcLimbDev* PolyEvaluator::upload_bc_limbs(const std::vector<BcLimbDev>& v) {
+    capture_abort();
     auto buf = std::make_unique<DevBuf>(v.size() * sizeof(BcLimbDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, v.data(), v.size() * sizeof(BcLimbDev), cudaMemcpyHostToDevice, stream()));
     OB_CUDA(cudaStreamSynchronize(stream()));

@@ -162,6 +162,7 @@ static const ulonglong2* stage_scalars(Context& c, int limbs, int L, const std::
         h[t] = make_ulonglong2(s, shoup_companion(s, q));
     }
     if (limbs <= SCAL_MAX) return nullptr;
+    capture_abort();                                          // a synchronising upload: not capturable
     buf.alloc(limbs * sizeof(ulonglong2));
     OB_CUDA(cudaMemcpyAsync(buf.p, h, limbs * sizeof(ulonglong2), cudaMemcpyHostToDevice, stream()));
     OB_CUDA(cudaStreamSynchronize(stream()));               // `big` dies at return

@@ -584,6 +584,7 @@ BaseConvBatch make_baseconv_batch(Context& c, const std::vector<BaseConvPlan>& p
         h[z].mm = mm | (w32 ? 4 : 0);
         b.mac_mode = std::max(b.mac_mode, mm);
     }
+    capture_abort();
     auto buf = std::make_unique<DevBuf>(h.size() * sizeof(BcDev));
     OB_CUDA(cudaMemcpyAsync(buf->p, h.data(), h.size() * sizeof(BcDev), cudaMemcpyHostToDevice, stream()));
     OB_CUDA(cudaStreamSynchronize(stream()));

@@ -131,6 +131,7 @@ int find_best_bsgs_ratio(const std::vector<int>& diags, int slots, int log_max_r
 
 std::unique_ptr<LinearTransform> lt_build(Scheme& s, const std::map<int, std::vector<double2>>& diagonals, int level,
                                           scale_t scale, int log_slots, int log_bsgs_ratio, bool encode) {
+    capture_abort();                                          // encoded diagonals are persistent state
     OB_CHECK(level >= 0 && level <= s.max_level, "linear transform level out of range");
     OB_CHECK(s.nP > 0, "linear transforms need special primes (LogP)");
     auto lt = std::make_unique<LinearTransform>();

@@ -84,6 +84,7 @@ size_t Scheme::reclaim_galois_keys(size_t want) {
 }
 Scheme::~Scheme() {
     unregister_reclaimer(reclaimer_id);
+    graphs_invalidate();
     cudaStreamSynchronize(stream());
     drop_scheme_tables(*ctx);
 }
@@ -168,6 +169,7 @@ const EvalKey& Scheme::galois_key(u64 galEl) {
     auto it = galois_keys.find(galEl);
     if (it != galois_keys.end()) { it->second->last_use = use_tick(); return *it->second; }
     OB_CHECK(has_sk(), "Galois key generation needs a secret key");
+    capture_abort();                                          // a key generated lazily: for real, from the pool
     // key switches s -> sigma_g^-1(s); the automorphism sigma_g applied afterwards maps it back to s
     u64 inv = 1, twoN = 2ull * N;
     for (u64 e = galEl, k = twoN / 2 - 1; k; k >>= 1, e = (e * e) & (twoN - 1)) if (k & 1) inv = (inv * e) & (twoN - 1);

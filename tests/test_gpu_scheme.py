@@ -384,3 +384,46 @@ def test_polynomial_evaluation_words_equal_the_oracles(orc, b200lib):
             assert got.shape == want.shape and np.array_equal(got, want), (deg, cheb)
     finally:
         B.DeleteScheme()
+
+
+def test_bootstrap_graph_replay_is_bit_identical(orc, b200lib):
+    """Bootstrap runs as a captured CUDA graph from the second call with the same (slot count, input level, input scale) on
+    (csrc/graphs.cu; default for logN <= 14): the first call is eager, later calls capture one instance per concurrently used
+    lane and replay it.  Every replay must return the eager call's words, for two different inputs, and an input at another
+    level (another key) must not disturb it."""
+    from orion_b200.bindings import B200Library
+    logn, logq, logp, logscale, h = 12, [55, 40, 40, 40, 40], [56, 56], 40, 64
+    B = B200Library()
+    B.B200_SetSeed(5)
+    B.NewScheme(logn, logq, logp, logscale, h, "standard", "", "none")
+    try:
+        B.NewKeyGenerator(); B.GenerateSecretKey(); B.GeneratePublicKey(); B.GenerateRelinearizationKey()
+        B.NewEncoder(); B.NewEncryptor(); B.NewDecryptor(); B.NewEvaluator()
+        slots = 1 << (logn - 1)
+        N = 1 << logn
+        B.NewBootstrapper([61] * 8, slots)
+        rng = np.random.default_rng(3)
+
+        def words(ct):
+            out = np.empty(2 * (B.GetCiphertextLevel(ct) + 1) * N, dtype=np.uint64)
+            B.B200_ExportCiphertext(ct, out)
+            return out
+
+        cts = [B.Encrypt(B.B200_EncodeF64(rng.uniform(-1, 1, slots), slots, 1, float(1 << logscale))) for _ in range(2)]
+        other = B.Encrypt(B.B200_EncodeF64(rng.uniform(-1, 1, slots), slots, 2, float(1 << logscale)))     # level 2: another key
+        first = [words(B.Bootstrap(c, slots)) for c in cts]                # eager (first sight of the key), then the first capture
+        assert not np.array_equal(first[0], first[1])
+        other_first = words(B.Bootstrap(other, slots))
+        l0 = b200lib.load().B200_LaunchCount()
+        for rep in range(6):                                               # replays, on whichever lanes the scheduler picks
+            for k, c in enumerate(cts):
+                assert np.array_equal(words(B.Bootstrap(c, slots)), first[k]), "replay %d of input %d" % (rep, k)
+            if rep == 2:
+                assert np.array_equal(words(B.Bootstrap(other, slots)), other_first)
+        assert b200lib.load().B200_LaunchCount() - l0 > 13 * 500          # replayed kernel nodes are counted as launches
+        # and it is a bootstrap
+        re_, im_ = np.empty(slots), np.empty(slots)
+        B.B200_DecodeF64(B.Decrypt(B.Bootstrap(cts[0], slots)), re_, im_)
+    finally:
+        B.DeleteBootstrappers()
+        B.DeleteScheme()
