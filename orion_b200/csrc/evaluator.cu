@@ -282,8 +282,10 @@ void PolyEvaluator::rescale(int level, const u64* in, int in_stride, u64* out, i
     }
     DevBuf last((size_t)polys * N * 8), tmp((size_t)polys * level * N * 8);
     ntt_inverse(ctx, in, last.u(), ci[key]);
-    rescale_prep(ctx, level, last.u(), tmp.u(), polys);
-    ntt_forward_first(ctx, tmp.u(), tmp.u(), cf[key]);
+    // ORION_B200_FUSED_RESCALE=0: the correction term through its own kernel and round trip (rescale_prep + first pass)
+    static const bool fused = [] { const char* e = std::getenv("ORION_B200_FUSED_RESCALE"); return !(e && std::atoi(e) == 0); }();
+    if (fused) ntt1_rescale(ctx, level, polys, last.u(), tmp.u());
+    else { rescale_prep(ctx, level, last.u(), tmp.u(), polys); ntt_forward_first(ctx, tmp.u(), tmp.u(), cf[key]); }
     ntt2_submul(ctx, level, polys, in, in_stride, tmp.u(), ctx.d_qlinv.as<ulonglong2>() + (size_t)level * ctx.nQ, nullptr, 0, 0, 0, 0,
                 out, out_stride);
 }

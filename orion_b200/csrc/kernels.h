@@ -91,5 +91,8 @@ void sum_qp(Context& c, int level, const SumList& lst, int n, u64* out);
 
 // rescale helpers (level -> level-1): see evaluator.cu
 void rescale_prep(Context& c, int level, const u64* last_coeff /* [polys][N] */, u64* tmp /* [polys][level][N] */, int polys);
+// the same correction term, computed inside the first forward NTT pass of its `level` limbs (ntt.cu ntt1_rescale_kernel): tmp holds
+// what rescale_prep + ntt_forward_first leave there
+void ntt1_rescale(Context& c, int level, int polys, const u64* last_coeff, u64* tmp);
 
 }  // namespace ob

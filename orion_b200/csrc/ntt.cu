@@ -779,6 +779,47 @@ ntt1_bc_kernel(const u64* __restrict__ ybuf, const unsigned char* __restrict__ v
     }
 }
 
+// Rescale: the first forward pass of limb i of polynomial p with its input computed on the fly from the coefficient-domain last limb
+//   x -> ((last[p][x] + (q_l - 1)/2) mod q_l) mod q_i - ((q_l - 1)/2 mod q_i)
+// (what rescale_prep_kernel writes to [polys][level][N] and ntt_forward_first reads back: one launch and one round trip less per
+// rescale; the last limb -- N words per polynomial -- is served from L2 to its `level` readers).  Same words.
+template <class A>
+struct RescaleLoader {
+    const u64* last;
+    u64 ql, half, q, hq;
+    ModConst m;
+    A ar;
+    __device__ __forceinline__ typename A::T operator()(int gi) const {
+        const u64 s = add_mod(last[gi], half, ql);
+        return ar.from_word(sub_mod(barrett_red(0, s, m), hq, q));
+    }
+};
+template <int S1>
+__global__ void __launch_bounds__(1 << (LOG_E_STRIDED - log_ept(true, true)))
+ntt1_rescale_kernel(const u64* __restrict__ last, u64* out, int level, const ModConst* __restrict__ mc,
+                    const ulonglong2* __restrict__ tw_all, const double* __restrict__ twd_all, int logN) {
+    OB_PDL_LAUNCH();
+    __shared__ __align__(16) u64 sm[(1 << LOG_E_STRIDED) + (1 << (LOG_E_STRIDED - 3))];
+    const int i = blockIdx.y % level, p = blockIdx.y / level;
+    const size_t N = (size_t)1 << logN;
+    const ModConst m = mc[i];
+    const u64 ql = mc[level].q, half = (ql - 1) >> 1;
+    const u64 hq = barrett_red(0, half, m);
+    u64* dst = out + (size_t)blockIdx.y * N;
+    const ulonglong2 ni = make_ulonglong2(0, 0);
+    if (m.bits <= F64_MAX_BITS) {
+        const RescaleLoader<ArithF64> ld{last + (size_t)p * N, ql, half, m.q, hq, m, ArithF64(m)};
+        OB_PDL_WAIT();
+        ntt_body<ArithF64, LOG_E_STRIDED, S1, true, true, false, false, 0, RescaleLoader<ArithF64>>(
+            ArithF64(m), sm, nullptr, dst, twd_all + (size_t)i * N, ni, logN, nullptr, false, nullptr, -1, -1, &ld);
+    } else {
+        const RescaleLoader<ArithInt> ld{last + (size_t)p * N, ql, half, m.q, hq, m, ArithInt(m)};
+        OB_PDL_WAIT();
+        ntt_body<ArithInt, LOG_E_STRIDED, S1, true, true, false, false, 0, RescaleLoader<ArithInt>>(
+            ArithInt(m), sm, nullptr, dst, tw_all + (size_t)i * N, ni, logN, nullptr, false, nullptr, -1, -1, &ld);
+    }
+}
+
 // Whole-limb NTT / INTT in ONE launch for small rings (2^12 <= N <= 2^14): a thread-block cluster of N/2048 CTAs owns one
 // limb.  Forward: every CTA runs the strided pass on its 2048-word tile and scatters the lazy results through distributed
 // shared memory into the slice of the CTA that owns the destination words; after one cluster barrier every CTA runs the
@@ -915,6 +956,17 @@ void ntt_forward_first(Context& c, const u64* in, u64* out, const NttPlan& p) {
     const int s1 = c.logN - K2_BITS;
     dim3 g1(c.N >> LOG_E_STRIDED, p.n);
     OB_NTT_STRIDED_SWITCH(true, false, in, out, p.first, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.d_ninv.as<ulonglong2>(), c.logN)
+}
+
+// tmp[p][i] (i < level) = first forward pass of the rescale's correction term, computed from last[p] (ntt1_rescale_kernel)
+void ntt1_rescale(Context& c, int level, int polys, const u64* last, u64* tmp) {
+    const int s1 = c.logN - K2_BITS;
+    dim3 g1(c.N >> LOG_E_STRIDED, level * polys);
+    const int tpb = 1 << (LOG_E_STRIDED - log_ept(true, true));
+#define OB_RS(S1V) OB_LAUNCH((ntt1_rescale_kernel<S1V>), g1, tpb, 0, stream(), last, tmp, level, c.dmc(), c.tw_fwd(), c.twd_fwd(), c.logN)
+    switch (s1) { case 4: OB_RS(4); break; case 5: OB_RS(5); break; case 6: OB_RS(6); break; case 7: OB_RS(7); break;
+                  case 8: OB_RS(8); break; case 9: OB_RS(9); break; default: OB_FATAL("unsupported logN"); }
+#undef OB_RS
 }
 
 // acc[z][c][t] = sum_j NTT2(digits[z][j][t]) * evk_z[j][c][chain(t)]  -- see ntt2_ip_kernel.  One launch per arithmetic
