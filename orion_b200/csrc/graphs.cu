@@ -4,6 +4,9 @@
 
 namespace ob {
 
+static size_t g_graph_bytes = 0;                             // staging + scratch held by all live instances
+UnaryGraph::~UnaryGraph() { if (exec) cudaGraphExecDestroy(exec); if (done) cudaEventDestroy(done); g_graph_bytes -= held; }
+
 std::unique_ptr<Ciphertext> run_unary_graphed(Scheme& s, UnaryGraphSet& set, const Ciphertext& in, size_t arena_cap, const char* what,
                                               const std::function<std::unique_ptr<Ciphertext>(const Ciphertext&)>& eager) {
     if (g_capturing) return eager(in);                              // nested inside another captured sequence: part of that graph
@@ -27,8 +30,14 @@ std::unique_ptr<Ciphertext> run_unary_graphed(Scheme& s, UnaryGraphSet& set, con
     for (auto& gi : set.inst) if (gi->state > 0 && gi->last_stream == st) { pick = gi.get(); break; }
     if (!pick) for (auto& gi : set.inst) if (gi->state > 0 && (!gi->done || cudaEventQuery(gi->done) == cudaSuccess)) { pick = gi.get(); break; }
     cudaGetLastError();                                             // cudaErrorNotReady from the queries is not an error
-    if (!pick && set.inst.size() < 4) {
+    // every instance keeps its scratch for good: new instances stop when the graphs hold a quarter of the device's memory
+    // (a caller that walks through many distinct (level, scale) keys then simply runs the later ones eagerly)
+    static const size_t graph_budget = [] { size_t fr = 0, tot = 0; cudaMemGetInfo(&fr, &tot); return tot / 4; }();
+    const size_t want = (set.scratch ? std::max<size_t>((size_t)32 << 20, set.scratch * 5 / 2) : arena_cap) + in.data.bytes + set.out_bytes;
+    if (!pick && set.inst.size() < 4 && g_graph_bytes + want <= graph_budget) {
+        g_graph_bytes += want;
         set.inst.push_back(std::make_unique<UnaryGraph>());
+        set.inst.back()->held = want;
         // the arena reuses a block only on the stream that freed it and wastes up to half a block per reuse: 2.5 x the pool's
         // high-water mark of the eager call fits in practice (it doubles when it does not); `arena_cap` is the fallback
         pick = set.inst.back().get();

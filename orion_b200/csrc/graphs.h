@@ -29,8 +29,8 @@ struct UnaryGraph {
     cudaStream_t last_stream = nullptr;
     cudaEvent_t done = nullptr;                           // completion of the last launch (the result copy included)
     DevBuf in_stage, out_stage, arena;                    // persistent: input copy, result copy, scratch of the captured sequence
-    size_t arena_cap = 0;
-    ~UnaryGraph() { if (exec) cudaGraphExecDestroy(exec); if (done) cudaEventDestroy(done); }
+    size_t arena_cap = 0, held = 0;                       // `held`: its share of the graphs' memory budget (graphs.cu)
+    ~UnaryGraph();
 };
 struct UnaryGraphSet {
     int seen = 0;
